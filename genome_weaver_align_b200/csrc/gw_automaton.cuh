@@ -1,0 +1,287 @@
+// gw_automaton.cuh — resumable per-read driver around gw_search.cuh: AlignmentProcess.align_internal
+// (reference: align/src/main/java/org/utgenome/weaver/align/strategy/BidirectionalSuffixFilter.java:278-477) cut at the
+// points where the reference calls into the sampled suffix array and the verifier (verify :496-560). At those points the
+// read parks with up to two fragment requests; the locate and verify kernels fill them and the read resumes.
+#pragma once
+#include "gw_search.cuh"
+
+struct GwRoundQueues {
+    uint32_t* next_active;   // slots that parked in this round
+    uint32_t* locate_req;    // slot*2 + fragment
+    uint32_t* verify_req;    // slot*2 + fragment
+    uint32_t* counters;      // [0] n_next_active, [1] n_locate, [2] n_verify
+};
+
+__device__ __forceinline__ void gw_fail(GwReadCtx* c, int status) { c->status = status; c->phase = GW_PH_DONE; }
+
+// build QueryMask pattern masks (F and reversed R) of q[0], q[1]  (QueryMask.java:41-63; reads hold no N here)
+__device__ __forceinline__ void gw_build_masks(const GwSlab& s) {
+    GwReadCtx* c = s.ctx();
+    const int m = c->m, nb = (m + 63) >> 6;
+    for (int strand = 0; strand < 2; ++strand) {
+        for (int ch = 0; ch < 4; ++ch) {
+            u64* f = gw_mask_ptr(s, strand, 0, ch);
+            u64* r = gw_mask_ptr(s, strand, 1, ch);
+            for (int b = 0; b < GW_MAX_NB; ++b) { f[b] = 0; r[b] = 0; }
+            for (int b = 0; b < nb; ++b) {
+                u64 lo = c->qlo[strand][b], hi = c->qhi[strand][b];
+                u64 valid = (b == nb - 1 && (m & 63)) ? ((1ULL << (m & 63)) - 1ULL) : ~0ULL;
+                f[b] = ((ch & 2) ? hi : ~hi) & ((ch & 1) ? lo : ~lo) & valid;
+            }
+            // R bit (m-1-i) = F bit i : reverse the nb*64-bit string, then shift right by nb*64 - m
+            u64 rev[GW_MAX_NB];
+            for (int b = 0; b < nb; ++b) rev[b] = __brevll(f[nb - 1 - b]);
+            const int sh = nb * 64 - m;  // 0..63
+            for (int b = 0; b < nb; ++b) {
+                u64 v = rev[b] >> sh;
+                if (sh && b + 1 < nb) v |= rev[b + 1] << (64 - sh);
+                r[b] = v;
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ int gw_q_symbol(const GwReadCtx* c, int strand, int i) {
+    return (int)((((c->qhi[strand][i >> 6] >> (i & 63)) & 1ULL) << 1) | ((c->qlo[strand][i >> 6] >> (i & 63)) & 1ULL));
+}
+
+// reportAlignment request side: classify the fragments of the chain headed by `base`; returns true if the read must park
+__device__ __forceinline__ bool gw_begin_report(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, int32_t base,
+                                                const GwRoundQueues& rq) {
+    GwReadCtx* c = s.ctx();
+    c->pend_base = base;
+    int n = 0;
+    bool need = false;
+    for (int32_t o = base; o >= 0 && n < 2; o = gw_st(s, o)->next_split, ++n) {
+        const GwState* st = gw_st(s, o);
+        GwPendFrag* pf = &c->pend[n];
+        pf->state_off = o;
+        pf->res_abort = 0;
+        if (gw_is_clipped(st)) pf->kind = 0;
+        else if (!st->has_cur) pf->kind = 1;
+        else {
+            pf->kind = 2;
+            pf->sa_index = st->cur_lb;
+            // FMIndexOnGenome.toCoordinate: fm = ~(strand ^ (dir.isForward ? 0 : 1)) & 1
+            pf->fm = ~(gw_strand(st) ^ (gw_is_fwd(st) ? 0 : 1)) & 1;
+            uint32_t id = slot * 2u + (uint32_t)n;
+            rq.locate_req[atomicAdd(&rq.counters[1], 1u)] = id;
+            rq.verify_req[atomicAdd(&rq.counters[2], 1u)] = id;
+            need = true;
+        }
+    }
+    c->pend_n = n;
+    return need;
+}
+
+// reportAlignment completion: ReadHits from the verified fragments, sortSplits, AlignmentResultHolder.add
+__device__ __forceinline__ void gw_finish_report(const GwSearchEnv& env, const GwSlab& s) {
+    GwReadCtx* c = s.ctx();
+    const int k = c->k;
+    int32_t hits[2] = {-1, -1};
+    for (int f = 0; f < c->pend_n; ++f) {
+        GwPendFrag* pf = &c->pend[f];
+        const GwState* st = gw_st(s, pf->state_off);
+        const int strand = gw_strand(st);
+        int32_t h;
+        if (pf->kind == 0) {
+            uint32_t cg = ((uint32_t)gw_frag_len(st) << 4) | GW_OP_S;
+            h = gw_new_hit(s, GW_CHR_NULL, -1, 0, st->start, st->end, 0, strand, &cg, gw_frag_len(st) > 0 ? 1 : 0, 0);
+        } else if (pf->kind == 1) {
+            h = gw_new_hit(s, GW_CHR_EMPTY, 0, 0, 0, 0, 0, strand, nullptr, 0, 0);
+        } else {
+            if (pf->res_abort) { gw_fail(c, GW_ST_ABORT); return; }
+            c->n_sw++;
+            if (!pf->res_valid) h = gw_new_hit(s, GW_CHR_EMPTY, 0, 0, 0, 0, 0, strand, nullptr, 0, 0);
+            else {
+                int chr, pos;
+                if (!gw_translate(env.ix, pf->ref_start + pf->res_pos + 1, &chr, &pos)) { gw_fail(c, GW_ST_ABORT); return; }
+                h = gw_new_hit(s, chr, pos, gw_frag_len(st), st->start, st->end, pf->res_diff, strand, pf->cig, pf->res_cig_n,
+                               (int32_t)(st->cur_ub - st->cur_lb));
+            }
+        }
+        if (h < 0) { gw_fail(c, GW_ST_OVERFLOW); return; }
+        hits[f] = h;
+    }
+    if (c->pend_n == 2) gw_hit(s, hits[0])->next_split = hits[1];
+    GwHitNode* head = gw_hit(s, hits[0]);
+    if (gw_hit_total_match(s, head) == 0) return;
+    const int newK = gw_hit_total_diff(s, head);
+    if (newK > k) return;
+    gw_set_lower_k(gw_st(s, c->pend_base), newK);
+    int32_t first = hits[0];
+    if (c->pend_n == 2) {  // ReadHit.sortSplits on two fragments
+        GwHitNode* o1 = gw_hit(s, hits[0]);
+        GwHitNode* o2 = gw_hit(s, hits[1]);
+        int diff = 0;
+        bool anyNull = o1->chr == GW_CHR_NULL || o2->chr == GW_CHR_NULL;
+        if (anyNull) {
+            diff = o1->q_start - o2->q_start;
+            if (head->strand != 0) diff = -diff;
+        }
+        if (diff == 0) {
+            if (anyNull) { gw_fail(c, GW_ST_ABORT); return; }  // NullPointerException in the comparator
+            int r1 = o1->chr >= 0 ? env.ix.ctg_rank[o1->chr] : -1, r2 = o2->chr >= 0 ? env.ix.ctg_rank[o2->chr] : -1;
+            diff = r1 - r2;
+            if (diff == 0) diff = o1->pos - o2->pos;
+        }
+        if (diff > 0) { o2->next_split = hits[0]; o1->next_split = -1; first = hits[1]; }
+    }
+    if (!gw_add_result(s, env.cfg, first)) gw_fail(c, GW_ST_OVERFLOW);
+}
+
+// staircase table of the current minMismatches; returns nullptr and fails the read where the reference constructor throws
+__device__ __forceinline__ const u64* gw_staircase_for(const GwSearchEnv& env, GwReadCtx* c, int* kk) {
+    const int m = c->m, mm = c->min_mm;
+    *kk = mm;
+    if (mm < 0 || ((env.sf.abort_by_m[m] >> mm) & 1u)) { gw_fail(c, GW_ST_ABORT); return nullptr; }
+    const int nb = (m + 63) >> 6;
+    return env.sf.words + env.sf.base_by_m[m] + nb * (mm * (mm + 1) / 2);
+}
+
+// Runs one read until it finishes or parks. max_steps bounds the FM searches per call (0 = unbounded).
+__device__ __forceinline__ void gw_run_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq,
+                                            uint32_t* occ_lookups) {
+    GwReadCtx* c = s.ctx();
+    const int m = c->m, k = c->k;
+    const GwDevConfig& cfg = env.cfg;
+
+    if (c->phase == GW_PH_WAIT_EXACT) {  // reportExactMatchAlignment after the locate
+        const int strand = c->pend[0].state_off;
+        long long pos = strand == 0 ? (long long)env.ix.N - (long long)c->pend[0].textpos : (long long)c->pend[0].textpos;
+        if (strand == 0) pos -= m;
+        pos += 1;
+        int chr, p;
+        if (pos < 0 || !gw_translate(env.ix, pos, &chr, &p)) { gw_fail(c, GW_ST_ABORT); return; }
+        uint32_t cg = ((uint32_t)m << 4) | GW_OP_M;
+        int32_t h = gw_new_hit(s, chr, p, m, 0, m, 0, strand, &cg, 1, (int32_t)(c->scan_ub[strand] - c->scan_lb[strand]));
+        if (h < 0 || !gw_add_result(s, cfg, h)) { gw_fail(c, GW_ST_OVERFLOW); return; }
+        c->phase = GW_PH_DONE;
+        return;
+    }
+    if (c->phase == GW_PH_WAIT_VERIFY) {
+        c->phase = GW_PH_RUN;
+        gw_finish_report(env, s);
+        if (c->phase == GW_PH_DONE) return;
+    }
+    if (c->phase == GW_PH_INIT) {
+        for (int strand = 0; strand < 2; ++strand) {
+            if (c->scan_mm[strand] == 0) {
+                c->min_mm = 0;
+                c->pend[0].state_off = strand;
+                c->pend[0].kind = 2;
+                c->pend[0].sa_index = c->scan_lb[strand];
+                c->pend[0].fm = strand == 0 ? 1 : 0;  // FMIndexOnGenome.toCoordinate(saIndex, strand)
+                c->pend_n = 1;
+                rq.locate_req[atomicAdd(&rq.counters[1], 1u)] = slot * 2u;
+                rq.next_active[atomicAdd(&rq.counters[0], 1u)] = slot;
+                c->phase = GW_PH_WAIT_EXACT;
+                return;
+            }
+        }
+        if (k == 0) { c->phase = GW_PH_DONE; return; }
+        gw_build_masks(s);
+        for (int strand = 0; strand < 2; ++strand) {
+            if (c->scan_mm[strand] <= k) {
+                int ls = c->scan_ls[strand];
+                int32_t st = (ls != 0 && ls < m) ? gw_initial_state(env, s, strand, GW_DIR_BF, 0, m, ls, ls, k, 0, c->scan_mm[strand])
+                                                 : gw_initial_state(env, s, strand, GW_DIR_F, 0, m, 0, 0, k, 0, c->scan_mm[strand]);
+                if (st < 0 || !gw_queue_add(s, cfg, st)) { gw_fail(c, GW_ST_OVERFLOW); return; }
+            }
+        }
+        c->phase = GW_PH_RUN;
+    }
+
+    const int fmIndexSearchUpperBound = m * 20;
+    while (c->qn > 0) {
+        if (c->n_fm > fmIndexSearchUpperBound) break;
+        const int32_t base = gw_queue_poll(s, cfg);
+        int32_t c_off = base;
+        {
+            int32_t next = c_off;
+            bool report = false;
+            for (;;) {
+                const GwState* ns = gw_st(s, next);
+                if (!(gw_has_hit(ns) || gw_is_clipped(ns) || gw_remaining(ns) == 0)) break;
+                if (ns->next_split < 0) { report = true; break; }
+                next = ns->next_split;
+            }
+            if (report) {
+                if (gw_begin_report(env, s, slot, base, rq)) {
+                    c->phase = GW_PH_WAIT_VERIFY;
+                    rq.next_active[atomicAdd(&rq.counters[0], 1u)] = slot;
+                    return;
+                }
+                gw_finish_report(env, s);
+                if (c->phase == GW_PH_DONE) return;
+                continue;
+            }
+            c_off = next;
+        }
+        GwState* cs = gw_st(s, c_off);
+        if (gw_is_finished(cs)) continue;
+        const int nm = gw_lower_k(cs);
+        if (nm > c->min_mm) { c->n_cut++; continue; }
+        if (c->min_mm - nm < 0) continue;
+        {
+            int scoreUB = gw_score(s, cfg, gw_st(s, base), true);
+            if (scoreUB < 0 || scoreUB < c->best_score) { c->n_cut++; continue; }
+        }
+        const int strand = gw_strand(cs);
+        const int nextBase = gw_q_symbol(c, strand, gw_next_index(cs));
+        bool advanced = false;
+        if (!((cs->state >> nextBase) & 1)) {
+            cs->state |= 1 << nextBase;
+            if (!gw_si_is_empty(cs, nextBase)) {
+                GwSiSet nsi;
+                gw_next_si(env.ix, cs, nextBase, &nsi, occ_lookups);
+                c->n_fm++;
+                int kk;
+                const u64* tbl = gw_staircase_for(env, c, &kk);
+                if (!tbl) return;
+                int32_t ns = gw_next_state(env, s, c_off, nextBase, nsi, tbl, kk);
+                if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return; }
+                if (ns >= 0) {
+                    if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return; }
+                    advanced = true;
+                } else c->n_filt++;
+            }
+        }
+        if (advanced) continue;
+        {
+            int kk;
+            const u64* tbl = gw_staircase_for(env, c, &kk);
+            if (!tbl) return;
+            for (int ch = 0; ch < 4; ++ch) {
+                cs = gw_st(s, c_off);
+                if ((cs->state >> ch) & 1) continue;
+                cs->state |= 1 << ch;
+                if (gw_si_is_empty(cs, ch)) continue;
+                GwSiSet nsi;
+                gw_next_si(env.ix, cs, ch, &nsi, occ_lookups);
+                c->n_fm++;
+                int32_t ns = gw_next_state(env, s, c_off, ch, nsi, tbl, kk);
+                if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return; }
+                if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return; } }
+                else c->n_filt++;
+            }
+        }
+        cs = gw_st(s, c_off);
+        cs->state |= 1 << 4;
+        if (gw_num_split(s, gw_st(s, base)) < cfg.num_split_allowed && nm + 1 <= c->min_mm) {
+            const int index = gw_next_index(cs);
+            if (index > cfg.indel_end_skip && m - index >= cfg.indel_end_skip) {
+                int32_t ns = gw_split_state(env, s, c_off, k, false);
+                if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return; }
+                if (ns == -3) { gw_fail(c, GW_ST_ABORT); return; }
+                if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return; } }
+                else c->n_filt++;
+                int32_t cl = gw_split_state(env, s, c_off, k, true);
+                if (cl == -2) { gw_fail(c, GW_ST_OVERFLOW); return; }
+                if (cl == -3) { gw_fail(c, GW_ST_ABORT); return; }
+                if (cl >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, cl))) { gw_fail(c, GW_ST_OVERFLOW); return; } }
+            }
+        }
+    }
+    c->phase = GW_PH_DONE;
+}

@@ -1,0 +1,172 @@
+// gw_state.cuh — per-read work area ("slab") in HBM and the value types of the BSF search:
+// cursor, suffix-interval set, NFA rows, search state, priority queue, hit list.
+// Replaces (reference, align/src/main/java/org/utgenome/weaver/align/): strategy/Cursor.java:40-198,
+// SiSet.java:34-196, strategy/ReadAlignmentNFA.java:63-215, strategy/StaircaseFilter.java:91-102,
+// QueryMask.java:73-97, BitVector.java:106-116, strategy/BidirectionalSuffixFilter.java:133-165 (StateQueue),
+// :658-877 (SearchState), record/ReadHit.java:42-184.
+//
+// Object identity matters in the reference (states are mutated while aliased from several queue entries and
+// split chains), so states live in a bump-allocated arena and are referred to by word offsets, never copied.
+#pragma once
+#include "gw_fm.cuh"
+
+// ---- slab layout (8-byte words) -------------------------------------------------------------------------
+struct GwPendFrag {
+    int32_t state_off;   // arena offset of the fragment's SearchState
+    int32_t kind;        // 0 clipped, 1 no hit (currentSi == null), 2 needs locate+verify
+    uint32_t sa_index;   // currentSi.lowerBound
+    int32_t fm;          // index used by toCoordinate: 0 forward, 1 reverse
+    uint32_t textpos;    // SparseSuffixArray.get result (written by the locate kernel)
+    int32_t res_valid;   // 0: alignBlockDetailed returned null
+    int32_t res_pos, res_diff, res_cig_n;
+    int32_t res_abort;   // the reference would throw while verifying this fragment
+    long long ref_start; // window start (verify kernel)
+    uint32_t cig[GW_CIG_CAP];
+};
+
+struct GwReadCtx {
+    int32_t m, k;
+    int32_t min_mm, max_match_len, best_score;
+    int32_t n_fm, n_sw, n_cut, n_filt;
+    int32_t qn, top, phase, status;
+    int32_t n_hits;
+    int32_t scan_mm[2], scan_ls[2], scan_le[2];
+    uint32_t scan_lb[2], scan_ub[2];
+    int32_t pend_base, pend_n;
+    int32_t count_n, pad0;
+    GwPendFrag pend[2];
+    u64 qlo[2][GW_MAX_NB], qhi[2][GW_MAX_NB];  // q[0] = read, q[1] = its complement, N replaced by A in both
+};
+
+#define GW_CTX_WORDS ((uint32_t)((sizeof(GwReadCtx) + 7) / 8))
+#define GW_MASK_WORDS (2u * 2u * 4u * GW_MAX_NB)  // [strand][F/R][base][block]
+
+struct GwSlab {
+    u64* base;
+    GwSlabParams sp;
+    __device__ __forceinline__ GwReadCtx* ctx() const { return reinterpret_cast<GwReadCtx*>(base); }
+    __device__ __forceinline__ u64* masks() const { return base + GW_CTX_WORDS; }
+    __device__ __forceinline__ int32_t* queue() const { return reinterpret_cast<int32_t*>(base + GW_CTX_WORDS + GW_MASK_WORDS); }
+    __device__ __forceinline__ int32_t* hits() const { return queue() + sp.queue_cap; }
+    __device__ __forceinline__ uint32_t arena_begin() const { return GW_CTX_WORDS + GW_MASK_WORDS + (sp.queue_cap + sp.hit_cap + 1) / 2; }
+    __device__ __forceinline__ u64* at(int32_t off) const { return base + off; }
+};
+
+__device__ __forceinline__ u64* gw_mask_ptr(const GwSlab& s, int strand, int rev, int ch) {
+    return s.masks() + (((strand * 2 + rev) * 4 + ch) * GW_MAX_NB);
+}
+
+// ---- search state node --------------------------------------------------------------------------------
+// si_kind: SiSet subclass
+#define GW_SI_NULL 0
+#define GW_SI_EMPTY 1
+#define GW_SI_F 2
+#define GW_SI_B 3
+#define GW_SI_BD 4
+
+#define GW_DIR_F 0
+#define GW_DIR_B 1
+#define GW_DIR_BF 2
+
+struct GwState {
+    int16_t start, end, cursor, pivot;   // Cursor
+    uint8_t cflag;                       // strand | dir << 1
+    uint8_t si_kind;
+    uint8_t f_valid, b_valid;            // non-null entries of siF / siB (bit per base)
+    uint8_t height;                      // NFA rows; 0 with has_nfa == 0 means null automaton
+    uint8_t k_offset;
+    uint8_t has_cur;                     // currentSi != null
+    uint8_t has_nfa;
+    int32_t state;                       // packed flags as in SearchState.state
+    int32_t next_split;                  // arena offset, -1 == null
+    uint32_t cur_lb, cur_ub;
+    uint32_t sif[4][2], sib[4][2];
+    // followed by `height` u64 NFA rows
+};
+#define GW_STATE_WORDS ((uint32_t)((sizeof(GwState) + 7) / 8))
+
+__device__ __forceinline__ u64* gw_rows(GwState* s) { return reinterpret_cast<u64*>(s) + GW_STATE_WORDS; }
+__device__ __forceinline__ int gw_strand(const GwState* s) { return s->cflag & 1; }
+__device__ __forceinline__ int gw_dir(const GwState* s) { int d = (s->cflag >> 1) & 3; return d == 3 ? GW_DIR_F : d; }
+__device__ __forceinline__ bool gw_is_fwd(const GwState* s) { return gw_dir(s) != GW_DIR_B; }
+__device__ __forceinline__ int gw_frag_len(const GwState* s) { return s->end - s->start; }
+__device__ __forceinline__ int gw_processed(const GwState* s) { return gw_is_fwd(s) ? s->cursor - s->pivot : s->end - s->cursor; }
+__device__ __forceinline__ int gw_remaining(const GwState* s) { return gw_frag_len(s) - gw_processed(s); }
+__device__ __forceinline__ int gw_next_index(const GwState* s) { return gw_is_fwd(s) ? s->cursor : s->cursor - 1; }
+__device__ __forceinline__ int gw_head_offset(const GwState* s) {
+    int off = s->cursor - s->start;
+    if (gw_strand(s) == 1) off = gw_frag_len(s) - off;
+    return off;
+}
+__device__ __forceinline__ int gw_lower_k(const GwState* s) { return ((uint32_t)s->state >> 8) & 0xFF; }
+__device__ __forceinline__ void gw_set_lower_k(GwState* s, int d) { s->state = (s->state & ~(0xFF << 8)) | ((d & 0xFF) << 8); }
+__device__ __forceinline__ int gw_priority(const GwState* s) { return ((uint32_t)s->state >> 16) & 0xFF; }
+__device__ __forceinline__ bool gw_has_hit(const GwState* s) { return (((uint32_t)s->state >> 24) & 1) != 0; }
+__device__ __forceinline__ bool gw_is_clipped(const GwState* s) { return (((uint32_t)s->state >> 25) & 1) != 0; }
+__device__ __forceinline__ bool gw_is_finished(const GwState* s) { return (s->state & 0x1F) == 0x1F; }
+__device__ __forceinline__ int gw_current_acgt(const GwState* s) { int c = (s->state >> 5) & 7; return c > 4 ? 4 : c; }
+__device__ __forceinline__ int gw_pack_state(int ch, int minK, int prio, bool hasMatch) {
+    return ((ch & 7) << 5) | ((minK & 0xFF) << 8) | ((prio & 0xFF) << 16) | ((hasMatch ? 1 : 0) << 24);
+}
+
+// ---- ReadHit node -------------------------------------------------------------------------------------
+struct GwHitNode {
+    int32_t chr;          // contig id or GW_CHR_*
+    int32_t pos;
+    int32_t match_length, diff, strand, num_hits, q_start, q_end;
+    int32_t next_split;   // arena offset or -1
+    int32_t cig_n;
+    // followed by cig_n u32 cigar elements (BAM encoding)
+};
+#define GW_HIT_WORDS ((uint32_t)((sizeof(GwHitNode) + 7) / 8))
+__device__ __forceinline__ uint32_t* gw_hit_cigar(GwHitNode* h) { return reinterpret_cast<uint32_t*>(reinterpret_cast<u64*>(h) + GW_HIT_WORDS); }
+
+// bump allocation; returns -1 (and flags the read for the large-slab pass) on overflow
+__device__ __forceinline__ int32_t gw_alloc(const GwSlab& s, uint32_t words) {
+    GwReadCtx* c = s.ctx();
+    uint32_t top = (uint32_t)c->top;
+    if (top + words > s.sp.slab_words) return -1;
+    c->top = (int32_t)(top + words);
+    return (int32_t)top;
+}
+
+// ---- BitVector.substring64 over nb blocks -----------------------------------------------------------------
+__device__ __forceinline__ u64 gw_substring64(const u64* block, int nb, int start, int end) {
+    int pos = start / 64;
+    if (pos >= nb) return 0ULL;
+    int range = end - start;
+    u64 mask = (range >= 64) ? ~0ULL : ~jshl(~0ULL, range);
+    int offset = start % 64;
+    u64 low = jushr(block[pos], offset);
+    u64 high = (pos + 1 < nb) ? jshl(block[pos + 1] & ~jshl(~0ULL, offset), 64 - offset) : 0ULL;
+    return (high | low) & mask;
+}
+
+// QueryMask.getBidirectionalPatternMask64
+__device__ __forceinline__ u64 gw_pattern_mask64(const GwSlab& s, int strand, int m, bool dirIsForward, int nextIdx, int pivot,
+                                                 int cursor, int ch, int margin) {
+    const int nb = (m + 63) >> 6;
+    u64 p;
+    if (dirIsForward) {
+        const u64* f = gw_mask_ptr(s, strand, 0, ch);
+        int pos = nextIdx - margin;
+        if (pos < 0) p = jshl(gw_substring64(f, nb, 0, 64), -pos);
+        else p = gw_substring64(f, nb, pos, m);
+    } else {
+        const u64* r = gw_mask_ptr(s, strand, 1, ch);
+        int b = m - pivot;
+        int rshift = pivot - cursor - margin;
+        p = gw_substring64(r, nb, b, b + 64);
+        p = rshift >= 0 ? jushr(p, rshift) : jshl(p, -rshift);
+    }
+    return p;
+}
+
+// StaircaseFilter.getStairCaseMask64bit for the filter (m, kk); tbl points at the (kk+1) x nb words of that filter
+__device__ __forceinline__ u64 gw_staircase64(const u64* tbl, int m, int kk, int row, int offset) {
+    if (row >= kk + 1) return 0ULL;
+    const int nb = (m + 63) >> 6;
+    const u64* bv = tbl + row * nb;
+    if (offset >= 0) return jshl(~0ULL, m - offset) | gw_substring64(bv, nb, offset, offset + 64);
+    return jshl(gw_substring64(bv, nb, 0, 64), -offset);
+}

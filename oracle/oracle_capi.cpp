@@ -2,6 +2,7 @@
 // tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs. Never linked into the product.
 // Mirrors the reference's command flow: Align.execute / Align.query / PassReadToAligner
 // (align/src/main/java/org/utgenome/weaver/align/Align.java:76-140, :188-195) and SAMOutput (:51-82).
+#include <atomic>
 #include <chrono>
 #include <cstdlib>
 #include <thread>
@@ -88,12 +89,15 @@ int gwo_align(void* handle, const double* cfg, int n_reads, const char* names_jo
         if (nthreads < 1) nthreads = 1;
         std::vector<std::string> sam((size_t)n_reads);
         std::vector<uint64_t> occ((size_t)nthreads, 0);
+        std::atomic<int> next(0);
         auto t0 = std::chrono::steady_clock::now();
         auto work = [&](int tid) {
             BidirectionalSuffixFilter bsf(*h->fm, h->reference.get(), c);
             OccCounter::lookups = 0;
-            int lo = (int)((long long)n_reads * tid / nthreads), hi = (int)((long long)n_reads * (tid + 1) / nthreads);
-            for (int i = lo; i < hi; ++i) {
+            for (;;) {
+              int lo = next.fetch_add(64), hi = std::min(n_reads, lo + 64);  // dynamic chunks: per-read work has a heavy tail
+              if (lo >= n_reads) break;
+              for (int i = lo; i < hi; ++i) {
                 std::string& out = sam[(size_t)i];
                 int nl = 0;
                 try {
@@ -116,6 +120,7 @@ int gwo_align(void* handle, const double* cfg, int n_reads, const char* names_jo
                     out.clear(); nl = 0;
                 }
                 lines_per_read[i] = nl;
+              }
             }
             occ[(size_t)tid] = OccCounter::lookups;
         };
