@@ -12,10 +12,10 @@ struct GwRoundQueues {
     uint32_t* counters;      // [0] n_next_active, [1] n_locate, [2] n_verify
 };
 
-__device__ __forceinline__ void gw_fail(GwReadCtx* c, int status) { c->status = status; c->phase = GW_PH_DONE; }
+GW_HD void gw_fail(GwReadCtx* c, int status) { c->status = status; c->phase = GW_PH_DONE; }
 
 // build QueryMask pattern masks (F and reversed R) of q[0], q[1]  (QueryMask.java:41-63; reads hold no N here)
-__device__ __forceinline__ void gw_build_masks(const GwSlab& s) {
+GW_HD void gw_build_masks(const GwSlab& s) {
     GwReadCtx* c = s.ctx();
     const int m = c->m, nb = (m + 63) >> 6;
     for (int strand = 0; strand < 2; ++strand) {
@@ -30,7 +30,7 @@ __device__ __forceinline__ void gw_build_masks(const GwSlab& s) {
             }
             // R bit (m-1-i) = F bit i : reverse the nb*64-bit string, then shift right by nb*64 - m
             u64 rev[GW_MAX_NB];
-            for (int b = 0; b < nb; ++b) rev[b] = __brevll(f[nb - 1 - b]);
+            for (int b = 0; b < nb; ++b) rev[b] = gw_brev64(f[nb - 1 - b]);
             const int sh = nb * 64 - m;  // 0..63
             for (int b = 0; b < nb; ++b) {
                 u64 v = rev[b] >> sh;
@@ -41,12 +41,12 @@ __device__ __forceinline__ void gw_build_masks(const GwSlab& s) {
     }
 }
 
-__device__ __forceinline__ int gw_q_symbol(const GwReadCtx* c, int strand, int i) {
+GW_HD int gw_q_symbol(const GwReadCtx* c, int strand, int i) {
     return (int)((((c->qhi[strand][i >> 6] >> (i & 63)) & 1ULL) << 1) | ((c->qlo[strand][i >> 6] >> (i & 63)) & 1ULL));
 }
 
 // reportAlignment request side: classify the fragments of the chain headed by `base`; returns true if the read must park
-__device__ __forceinline__ bool gw_begin_report(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, int32_t base,
+GW_HD bool gw_begin_report(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, int32_t base,
                                                 const GwRoundQueues& rq) {
     GwReadCtx* c = s.ctx();
     c->pend_base = base;
@@ -65,8 +65,8 @@ __device__ __forceinline__ bool gw_begin_report(const GwSearchEnv& env, const Gw
             // FMIndexOnGenome.toCoordinate: fm = ~(strand ^ (dir.isForward ? 0 : 1)) & 1
             pf->fm = ~(gw_strand(st) ^ (gw_is_fwd(st) ? 0 : 1)) & 1;
             uint32_t id = slot * 2u + (uint32_t)n;
-            rq.locate_req[atomicAdd(&rq.counters[1], 1u)] = id;
-            rq.verify_req[atomicAdd(&rq.counters[2], 1u)] = id;
+            rq.locate_req[gw_atomic_add(&rq.counters[1], 1u)] = id;
+            rq.verify_req[gw_atomic_add(&rq.counters[2], 1u)] = id;
             need = true;
         }
     }
@@ -75,7 +75,7 @@ __device__ __forceinline__ bool gw_begin_report(const GwSearchEnv& env, const Gw
 }
 
 // reportAlignment completion: ReadHits from the verified fragments, sortSplits, AlignmentResultHolder.add
-__device__ __forceinline__ void gw_finish_report(const GwSearchEnv& env, const GwSlab& s) {
+GW_HD void gw_finish_report(const GwSearchEnv& env, const GwSlab& s) {
     GwReadCtx* c = s.ctx();
     const int k = c->k;
     int32_t hits[2] = {-1, -1};
@@ -86,13 +86,13 @@ __device__ __forceinline__ void gw_finish_report(const GwSearchEnv& env, const G
         int32_t h;
         if (pf->kind == 0) {
             uint32_t cg = ((uint32_t)gw_frag_len(st) << 4) | GW_OP_S;
-            h = gw_new_hit(s, GW_CHR_NULL, -1, 0, st->start, st->end, 0, strand, &cg, gw_frag_len(st) > 0 ? 1 : 0, 0);
+            h = gw_new_hit(s, GW_CHR_NULL_, -1, 0, st->start, st->end, 0, strand, &cg, 1, 0);
         } else if (pf->kind == 1) {
-            h = gw_new_hit(s, GW_CHR_EMPTY, 0, 0, 0, 0, 0, strand, nullptr, 0, 0);
+            h = gw_new_hit(s, GW_CHR_EMPTY_, 0, 0, 0, 0, 0, strand, nullptr, 0, 0);
         } else {
-            if (pf->res_abort) { gw_fail(c, GW_ST_ABORT); return; }
+            if (pf->res_abort) { gw_fail(c, pf->res_abort == 2 ? GW_ST_UNSUPPORTED : GW_ST_ABORT); return; }
             c->n_sw++;
-            if (!pf->res_valid) h = gw_new_hit(s, GW_CHR_EMPTY, 0, 0, 0, 0, 0, strand, nullptr, 0, 0);
+            if (!pf->res_valid) h = gw_new_hit(s, GW_CHR_EMPTY_, 0, 0, 0, 0, 0, strand, nullptr, 0, 0);
             else {
                 int chr, pos;
                 if (!gw_translate(env.ix, pf->ref_start + pf->res_pos + 1, &chr, &pos)) { gw_fail(c, GW_ST_ABORT); return; }
@@ -114,7 +114,7 @@ __device__ __forceinline__ void gw_finish_report(const GwSearchEnv& env, const G
         GwHitNode* o1 = gw_hit(s, hits[0]);
         GwHitNode* o2 = gw_hit(s, hits[1]);
         int diff = 0;
-        bool anyNull = o1->chr == GW_CHR_NULL || o2->chr == GW_CHR_NULL;
+        bool anyNull = o1->chr == GW_CHR_NULL_ || o2->chr == GW_CHR_NULL_;
         if (anyNull) {
             diff = o1->q_start - o2->q_start;
             if (head->strand != 0) diff = -diff;
@@ -131,7 +131,7 @@ __device__ __forceinline__ void gw_finish_report(const GwSearchEnv& env, const G
 }
 
 // staircase table of the current minMismatches; returns nullptr and fails the read where the reference constructor throws
-__device__ __forceinline__ const u64* gw_staircase_for(const GwSearchEnv& env, GwReadCtx* c, int* kk) {
+GW_HD const u64* gw_staircase_for(const GwSearchEnv& env, GwReadCtx* c, int* kk) {
     const int m = c->m, mm = c->min_mm;
     *kk = mm;
     if (mm < 0 || ((env.sf.abort_by_m[m] >> mm) & 1u)) { gw_fail(c, GW_ST_ABORT); return nullptr; }
@@ -140,9 +140,9 @@ __device__ __forceinline__ const u64* gw_staircase_for(const GwSearchEnv& env, G
 }
 
 // Runs one read until it finishes or parks. max_steps bounds the FM searches per call (0 = unbounded).
-__device__ __forceinline__ void gw_run_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq,
-                                            uint32_t* occ_lookups) {
+GW_HD void gw_run_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
     GwReadCtx* c = s.ctx();
+    uint32_t* occ_lookups = &c->occ_search;
     const int m = c->m, k = c->k;
     const GwDevConfig& cfg = env.cfg;
 
@@ -173,8 +173,8 @@ __device__ __forceinline__ void gw_run_read(const GwSearchEnv& env, const GwSlab
                 c->pend[0].sa_index = c->scan_lb[strand];
                 c->pend[0].fm = strand == 0 ? 1 : 0;  // FMIndexOnGenome.toCoordinate(saIndex, strand)
                 c->pend_n = 1;
-                rq.locate_req[atomicAdd(&rq.counters[1], 1u)] = slot * 2u;
-                rq.next_active[atomicAdd(&rq.counters[0], 1u)] = slot;
+                rq.locate_req[gw_atomic_add(&rq.counters[1], 1u)] = slot * 2u;
+                rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
                 c->phase = GW_PH_WAIT_EXACT;
                 return;
             }
@@ -209,7 +209,7 @@ __device__ __forceinline__ void gw_run_read(const GwSearchEnv& env, const GwSlab
             if (report) {
                 if (gw_begin_report(env, s, slot, base, rq)) {
                     c->phase = GW_PH_WAIT_VERIFY;
-                    rq.next_active[atomicAdd(&rq.counters[0], 1u)] = slot;
+                    rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
                     return;
                 }
                 gw_finish_report(env, s);

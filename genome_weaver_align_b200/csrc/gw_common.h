@@ -1,14 +1,29 @@
 // gw_common.h — structures shared by host and device code of libgwalign.so.
+//
 // Data layout in HBM (DESIGN.md "Data layout"):
-//   occ block (64 B, one per 128 BWT symbols, 64 B aligned):
-//     u32 cnt[4]   occurrences of A,C,G,T in BWT[0, 128*b)           (16 B)
-//     u64 lo[2]    low  bit of the 2-bit code, bit j = symbol 128*b+j (16 B)
-//     u64 hi[2]    high bit of the 2-bit code                          (16 B)
-//     u64 nf[2]    N flag (N symbols are excluded from A/C/G/T counts) (16 B)
-//   This replaces OccurrenceCountTable.occTable + the BWT ACGTSequence (reference: OccurrenceCountTable.java:51-72,
-//   ACGTSequence.java:47-58) by one cache-line-aligned record, so a rank query touches exactly one 64 B line.
+//   occ block (64 B, one per 128 BWT symbols, 64 B aligned) = 4 quarters of 16 B; quarter q holds
+//     u32 cnt   occurrences of symbol q (A,C,G,T for q = 0..3) in BWT[0, 128*b)
+//     u32 lo    low  bit of the 2-bit code of symbols 128*b+32*q .. +31 (bit j = symbol 32*q+j)
+//     u32 hi    high bit of the 2-bit code
+//     u32 nf    N flag (N symbols are excluded from the A/C/G/T counts)
+//   Every quarter is self-contained, so a rank query can be served either by one thread with four 128-bit loads
+//   or by four lanes with one 128-bit load each (one 64 B line per query either way).
+//   This replaces OccurrenceCountTable.occTable + the BWT ACGTSequence of the reference
+//   (align/src/main/java/org/utgenome/weaver/align/OccurrenceCountTable.java:51-72, ACGTSequence.java:47-58).
+//
+// The per-thread bodies of all kernels are written as GW_HD functions: nvcc compiles them for sm_100a; the test-only
+// host simulator (tests/hostsim) compiles the same headers with g++ to check the automaton logic without a GPU.
 #pragma once
 #include <stdint.h>
+#include <string.h>
+
+#if defined(__CUDACC__)
+#define GW_HD __host__ __device__ __forceinline__
+#else
+#define GW_HD inline
+#endif
+
+typedef unsigned long long u64;
 
 #define GW_MAX_READ_LEN 256
 #define GW_MAX_NB 4          // ceil(GW_MAX_READ_LEN / 64)
@@ -18,10 +33,24 @@
 #define GW_CIG_CAP 36        // cigar elements kept per verified fragment (>= 2*GW_MAX_K + 3)
 #define GW_MAX_WINDOW (GW_MAX_READ_LEN + 2 * GW_MAX_K + 2)
 
-struct GwOccBlock {
-    uint32_t cnt[4];
-    uint64_t lo[2], hi[2], nf[2];
-};
+// special chr ids / status codes (mirrored in include/gw_align.h)
+#define GW_CHR_NULL_ (-1)
+#define GW_CHR_EMPTY_ (-2)
+#define GW_CHR_STAR_ (-3)
+#define GW_ST_OK 0
+#define GW_ST_UNMAPPED 1
+#define GW_ST_ABORT 2
+#define GW_ST_UNSUPPORTED 3
+#define GW_ST_OVERFLOW 100   // internal: slab too small, rerun in the large-slab pass
+
+#define GW_OP_M 0u
+#define GW_OP_I 1u
+#define GW_OP_D 2u
+#define GW_OP_S 4u
+
+struct GwU4 { uint32_t x, y, z, w; };
+struct GwOccBlock { GwU4 q[4]; };   // q[i] = {cnt_i, lo, hi, nf}
+struct GwU64x2 { u64 x, y; };
 
 // device view of an opened index
 struct GwIndexView {
@@ -30,11 +59,11 @@ struct GwIndexView {
     uint32_t C[2][5];           // CharacterCount.C per index
     uint32_t N;                 // text length (all contigs concatenated)
     uint32_t n_ssa;
-    // forward reference text as bit planes (verification windows), one u64 per 64 bases
-    const uint64_t* ref_lo;
-    const uint64_t* ref_hi;
-    const uint64_t* ref_nf;
-    // contig table for SequenceBoundary.translate: distinct offsets ascending, the contig id owning each, name order rank
+    // forward reference text as bit planes (verification windows), one u64 per 64 bases, bit j = base 64*w+j
+    const u64* ref_lo;
+    const u64* ref_hi;
+    const u64* ref_nf;
+    // contig table for SequenceBoundary.translate: distinct offsets ascending, the contig id owning each
     const uint32_t* ctg_off;
     const int32_t* ctg_id;
     const int32_t* ctg_rank;    // by contig id: rank of its name under java.lang.String.compareTo (equal names share a rank)
@@ -50,7 +79,7 @@ struct GwDevConfig {
     int32_t num_split_allowed, match_score, mismatch_penalty, split_open_penalty, indel_end_skip, band_width, report_type, top_l;
 };
 
-// per-wave slab geometry (one slab per read; see gw_device.cuh)
+// per-wave slab geometry (one slab per read; see gw_state.cuh)
 struct GwSlabParams {
     uint32_t slab_words;   // size of one read slab in 8-byte words
     uint32_t queue_cap;    // max live states in the priority queue
@@ -59,7 +88,7 @@ struct GwSlabParams {
 
 // staircase filter tables for every read length present in a batch
 struct GwStaircaseView {
-    const uint64_t* words;      // all tables
+    const u64* words;           // all tables
     const int32_t* base_by_m;   // [GW_MAX_READ_LEN+1] word offset of the table set of length m, -1 if absent
     const uint32_t* abort_by_m; // [GW_MAX_READ_LEN+1] bit kk set: the reference throws when constructing StaircaseFilter(m, kk)
 };
@@ -71,3 +100,64 @@ enum GwPhase : int32_t {
     GW_PH_WAIT_VERIFY = 3, // parked: a chain waits for locate + verification of its fragments
     GW_PH_DONE = 4
 };
+
+// ---- portability shims (device intrinsics / host builtins) ------------------------------------------------
+GW_HD int gw_popc32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __popc(x);
+#else
+    return __builtin_popcount(x);
+#endif
+}
+GW_HD int gw_popc64(u64 x) {
+#if defined(__CUDA_ARCH__)
+    return __popcll(x);
+#else
+    return __builtin_popcountll(x);
+#endif
+}
+GW_HD u64 gw_brev64(u64 x) {
+#if defined(__CUDA_ARCH__)
+    return __brevll(x);
+#else
+    u64 r = 0;
+    for (int i = 0; i < 64; ++i) r |= ((x >> i) & 1ULL) << (63 - i);
+    return r;
+#endif
+}
+GW_HD GwU4 gw_ld128(const GwU4* p) {
+#if defined(__CUDA_ARCH__)
+    uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+    GwU4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w;
+    return r;
+#else
+    return *p;
+#endif
+}
+GW_HD uint32_t gw_ld32(const uint32_t* p) {
+#if defined(__CUDA_ARCH__)
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
+GW_HD u64 gw_ld64(const u64* p) {
+#if defined(__CUDA_ARCH__)
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
+GW_HD uint32_t gw_atomic_add(uint32_t* p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+    return atomicAdd(p, v);
+#else
+    return __atomic_fetch_add(p, v, __ATOMIC_RELAXED);
+#endif
+}
+GW_HD int gw_max(int a, int b) { return a > b ? a : b; }
+GW_HD int gw_min(int a, int b) { return a < b ? a : b; }
+
+// Java shift semantics (count & 63)
+GW_HD u64 jshl(u64 x, int s) { return x << (s & 63); }
+GW_HD u64 jushr(u64 x, int s) { return x >> (s & 63); }

@@ -3,106 +3,97 @@
 //   OccurrenceCountTable.getOccACGTN :80-89, getOcc :99-107; ACGTSequence.fastCount(ACGTN) :456-553
 //   FMIndexOnOccTable.backwardSearch :47-51, suffixLink :64-70; SparseSuffixArray.get :141-161
 //   SequenceBoundary.translate :104-121
+// These are the single-thread forms (one thread fetches the whole 64 B line with four 128-bit loads); the quick-scan
+// and locate kernels in gw_kernels.cu also have 4-lane cooperative forms built on gw_quarter_*.
 #pragma once
-#include <cuda_runtime.h>
-
 #include "gw_common.h"
 
-typedef unsigned long long u64;
+struct GwBlk { GwU4 q[4]; };
 
-// Java shift semantics (count & 63)
-__device__ __forceinline__ u64 jshl(u64 x, int s) { return x << (s & 63); }
-__device__ __forceinline__ u64 jushr(u64 x, int s) { return x >> (s & 63); }
-
-struct GwBlockRegs {
-    uint4 c;   // cnt A,C,G,T
-    u64 lo0, lo1, hi0, hi1, nf0, nf1;
-};
-
-// one 64-byte line as four 128-bit read-only loads
-__device__ __forceinline__ GwBlockRegs gw_load_block(const GwOccBlock* blk) {
-    const uint4* p = reinterpret_cast<const uint4*>(blk);
-    uint4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2), d = __ldg(p + 3);
-    GwBlockRegs r;
-    r.c = a;
-    r.lo0 = ((u64)b.y << 32) | b.x; r.lo1 = ((u64)b.w << 32) | b.z;
-    r.hi0 = ((u64)c.y << 32) | c.x; r.hi1 = ((u64)c.w << 32) | c.z;
-    r.nf0 = ((u64)d.y << 32) | d.x; r.nf1 = ((u64)d.w << 32) | d.z;
-    return r;
+GW_HD GwBlk gw_load_block(const GwOccBlock* blk) {
+    GwBlk b;
+    b.q[0] = gw_ld128(&blk->q[0]); b.q[1] = gw_ld128(&blk->q[1]);
+    b.q[2] = gw_ld128(&blk->q[2]); b.q[3] = gw_ld128(&blk->q[3]);
+    return b;
 }
 
-// prefix masks for the first r (0..127) symbols of a block
-__device__ __forceinline__ void gw_prefix_masks(uint32_t r, u64& m0, u64& m1) {
-    m0 = r >= 64 ? ~0ULL : ((1ULL << r) - 1ULL);
-    m1 = r > 64 ? ((1ULL << (r - 64)) - 1ULL) : 0ULL;
+// mask of the symbols of quarter q that lie in the block prefix [0, r), r in 0..127
+GW_HD uint32_t gw_quarter_mask(uint32_t r, int q) {
+    int n = (int)r - 32 * q;
+    return n <= 0 ? 0u : (n >= 32 ? 0xFFFFFFFFu : ((1u << n) - 1u));
+}
+// occurrences of symbol ch (0..3) among the prefix symbols of one quarter (N-flagged symbols excluded)
+GW_HD uint32_t gw_quarter_count1(const GwU4& qd, uint32_t mask, int ch) {
+    uint32_t h = (ch & 2) ? qd.z : ~qd.z, l = (ch & 1) ? qd.y : ~qd.y;
+    return (uint32_t)gw_popc32(h & l & ~qd.w & mask);
 }
 
 // occurrences of A,C,G,T (N-flagged symbols excluded) in BWT[0, i)  == getOccACGTN without the N column
-__device__ __forceinline__ void gw_rank4(const GwBlockRegs& b, uint32_t r, uint32_t out[4]) {
-    u64 m0, m1;
-    gw_prefix_masks(r, m0, m1);
-    u64 v0 = ~b.nf0 & m0, v1 = ~b.nf1 & m1;
-    uint32_t t = __popcll(b.hi0 & b.lo0 & v0) + __popcll(b.hi1 & b.lo1 & v1);
-    uint32_t g = __popcll(b.hi0 & ~b.lo0 & v0) + __popcll(b.hi1 & ~b.lo1 & v1);
-    uint32_t c = __popcll(~b.hi0 & b.lo0 & v0) + __popcll(~b.hi1 & b.lo1 & v1);
-    uint32_t a = __popcll(v0) + __popcll(v1) - t - g - c;
-    out[0] = b.c.x + a; out[1] = b.c.y + c; out[2] = b.c.z + g; out[3] = b.c.w + t;
+GW_HD void gw_rank4(const GwBlk& b, uint32_t r, uint32_t out[4]) {
+    uint32_t a = 0, c = 0, g = 0, t = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint32_t lo = b.q[q].y, hi = b.q[q].z;
+        const uint32_t v = ~b.q[q].w & gw_quarter_mask(r, q);
+        const uint32_t tt = (uint32_t)gw_popc32(hi & lo & v), gg = (uint32_t)gw_popc32(hi & ~lo & v), cc = (uint32_t)gw_popc32(~hi & lo & v);
+        t += tt; g += gg; c += cc; a += (uint32_t)gw_popc32(v) - tt - gg - cc;
+    }
+    out[0] = b.q[0].x + a; out[1] = b.q[1].x + c; out[2] = b.q[2].x + g; out[3] = b.q[3].x + t;
 }
 
 // occurrences of one symbol ch (0..3) in BWT[0, i)
-__device__ __forceinline__ uint32_t gw_rank1(const GwBlockRegs& b, uint32_t r, int ch) {
-    u64 m0, m1;
-    gw_prefix_masks(r, m0, m1);
-    u64 h0 = (ch & 2) ? b.hi0 : ~b.hi0, h1 = (ch & 2) ? b.hi1 : ~b.hi1;
-    u64 l0 = (ch & 1) ? b.lo0 : ~b.lo0, l1 = (ch & 1) ? b.lo1 : ~b.lo1;
-    uint32_t n = __popcll(h0 & l0 & ~b.nf0 & m0) + __popcll(h1 & l1 & ~b.nf1 & m1);
-    uint32_t base = ch == 0 ? b.c.x : ch == 1 ? b.c.y : ch == 2 ? b.c.z : b.c.w;
+GW_HD uint32_t gw_rank1(const GwBlk& b, uint32_t r, int ch) {
+    uint32_t n = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) n += gw_quarter_count1(b.q[q], gw_quarter_mask(r, q), ch);
+    const uint32_t base = ch == 0 ? b.q[0].x : ch == 1 ? b.q[1].x : ch == 2 ? b.q[2].x : b.q[3].x;
     return base + n;
 }
 
 // number of N in BWT[0, i): block start minus the four counters, plus N flags in the prefix
-__device__ __forceinline__ uint32_t gw_rankN(const GwBlockRegs& b, uint32_t blockStart, uint32_t r) {
-    u64 m0, m1;
-    gw_prefix_masks(r, m0, m1);
-    return blockStart - (b.c.x + b.c.y + b.c.z + b.c.w) + __popcll(b.nf0 & m0) + __popcll(b.nf1 & m1);
+GW_HD uint32_t gw_rankN(const GwBlk& b, uint32_t blockStart, uint32_t r) {
+    uint32_t n = blockStart - (b.q[0].x + b.q[1].x + b.q[2].x + b.q[3].x);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) n += (uint32_t)gw_popc32(b.q[q].w & gw_quarter_mask(r, q));
+    return n;
 }
 
-__device__ __forceinline__ uint32_t gw_clampN(const GwIndexView& ix, uint32_t i) { return i > ix.N ? ix.N : i; }
+GW_HD uint32_t gw_clampN(const GwIndexView& ix, uint32_t i) { return i > ix.N ? ix.N : i; }
 
-// getOcc(ch, i) for ch in A,C,G,T
-__device__ __forceinline__ uint32_t gw_occ1(const GwIndexView& ix, int fm, int ch, uint32_t i) {
+// getOcc(ch, i) for ch in A,C,G,T (OccurrenceCountTable.java:99-107)
+GW_HD uint32_t gw_occ1(const GwIndexView& ix, int fm, int ch, uint32_t i) {
     i = gw_clampN(ix, i);
-    GwBlockRegs b = gw_load_block(ix.occ[fm] + (i >> 7));
+    GwBlk b = gw_load_block(ix.occ[fm] + (i >> 7));
     return gw_rank1(b, i & 127u, ch);
 }
 
 // FMIndexOnOccTable.suffixLink: one LF step
-__device__ __forceinline__ uint32_t gw_suffix_link(const GwIndexView& ix, int fm, uint32_t index) {
+GW_HD uint32_t gw_suffix_link(const GwIndexView& ix, int fm, uint32_t index) {
     if (index >= ix.N) return 0;
-    GwBlockRegs b = gw_load_block(ix.occ[fm] + (index >> 7));
-    uint32_t r = index & 127u;
-    u64 lo = r < 64 ? b.lo0 : b.lo1, hi = r < 64 ? b.hi0 : b.hi1, nf = r < 64 ? b.nf0 : b.nf1;
-    uint32_t s = r & 63u;
-    if ((nf >> s) & 1ULL) return ix.C[fm][4] + gw_rankN(b, index & ~127u, r);
-    int ch = (int)(((hi >> s) & 1ULL) << 1 | ((lo >> s) & 1ULL));
+    GwBlk b = gw_load_block(ix.occ[fm] + (index >> 7));
+    const uint32_t r = index & 127u;
+    const GwU4 qd = b.q[r >> 5];
+    const uint32_t s = r & 31u;
+    if ((qd.w >> s) & 1u) return ix.C[fm][4] + gw_rankN(b, index & ~127u, r);
+    const int ch = (int)((((qd.z >> s) & 1u) << 1) | ((qd.y >> s) & 1u));
     return ix.C[fm][ch] + gw_rank1(b, r, ch);
 }
 
 // SparseSuffixArray.get: text position of SA row `index`; *steps receives the number of LF steps (occ lookups)
-__device__ __forceinline__ uint32_t gw_sa_get(const GwIndexView& ix, int fm, uint32_t index, uint32_t* steps) {
+GW_HD uint32_t gw_sa_get(const GwIndexView& ix, int fm, uint32_t index, uint32_t* steps) {
     uint32_t cursor = index, j = 0;
     while ((cursor % GW_SSA_L) != 0) {
         cursor = gw_suffix_link(ix, fm, cursor);
         ++j;
     }
     *steps = j;
-    uint32_t s = __ldg(ix.ssa[fm] + cursor / GW_SSA_L);
+    const uint32_t s = gw_ld32(ix.ssa[fm] + cursor / GW_SSA_L);
     if (j == 0) return s;
     return (uint32_t)(((u64)s + j + ix.N) % ix.N);
 }
 
 // SequenceBoundary.translate(textIndex): greatest contig offset strictly below textIndex (TreeMap.headMap)
-__device__ __forceinline__ bool gw_translate(const GwIndexView& ix, long long textIndex, int* chr, int* pos) {
+GW_HD bool gw_translate(const GwIndexView& ix, long long textIndex, int* chr, int* pos) {
     int lo = 0, hi = ix.n_ctg_off;  // first offset >= textIndex
     while (lo < hi) {
         int mid = (lo + hi) >> 1;
@@ -115,8 +106,8 @@ __device__ __forceinline__ bool gw_translate(const GwIndexView& ix, long long te
 }
 
 // symbol (0..4) of the forward reference text at position p
-__device__ __forceinline__ int gw_ref_symbol(const GwIndexView& ix, uint32_t p) {
-    uint32_t w = p >> 6, s = p & 63u;
-    if ((__ldg(ix.ref_nf + w) >> s) & 1ULL) return 4;
-    return (int)((((__ldg(ix.ref_hi + w) >> s) & 1ULL) << 1) | ((__ldg(ix.ref_lo + w) >> s) & 1ULL));
+GW_HD int gw_ref_symbol(const GwIndexView& ix, uint32_t p) {
+    const uint32_t w = p >> 6, s = p & 63u;
+    if ((gw_ld64(ix.ref_nf + w) >> s) & 1ULL) return 4;
+    return (int)((((gw_ld64(ix.ref_hi + w) >> s) & 1ULL) << 1) | ((gw_ld64(ix.ref_lo + w) >> s) & 1ULL));
 }

@@ -1,0 +1,272 @@
+// gw_kernels.cu — the sm_100a kernels of the read-alignment path and their launchers.
+//
+//   kernel 1  gw_scan_coop_kernel   rank/occ + exact quick scan; 4 lanes share one 64 B occurrence block (one 128-bit
+//                                   load per lane), popcounts combined with warp shuffles   (FMQuickScan.java:66-94)
+//             gw_scan_kernel        single-thread form of the same scan (kept for A/B measurements)
+//   kernel 2  gw_search_kernel      per-read best-first bidirectional search automaton        (BidirectionalSuffixFilter.java:278-477)
+//   kernel 3  gw_locate_kernel      batched SA-sample locate (LF walk)                        (SparseSuffixArray.java:141-161)
+//   kernel 4  gw_verify_kernel      bit-vector DP verifier + CIGAR traceback                  (BitParallelSmithWaterman.java:387-644)
+//   plus prep (read encoding), emit (hit records) and small utility kernels.
+// Grids are sized from the work-list length; every kernel is HBM/L2 random-access or integer-pipe bound (no tensor cores:
+// nothing here is a dense contraction).
+#include <cuda_runtime.h>
+
+#include "gw_bodies.cuh"
+#include "gw_kernels.h"
+
+// ---------------------------------------------------------------------------------------------------------
+__global__ void gw_prep_kernel(GwBatchView bv, u64* const* slabs, const uint32_t* slots, uint32_t n, uint32_t read_base, GwSlabParams sp) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t slot = slots ? slots[i] : i;
+    gw_prep_read(bv, slabs[slot], sp, read_base + slot);
+}
+
+__global__ void gw_scan_kernel(GwIndexView ix, u64* const* slabs, const uint32_t* slots, uint32_t n_tasks) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tasks) return;
+    uint32_t slot = slots ? slots[t >> 1] : (t >> 1);
+    gw_scan_task(ix, reinterpret_cast<GwReadCtx*>(slabs[slot]), (int)(t & 1u));
+}
+
+// 4 lanes per (read, strand) task: lane q of the group loads quarter q of the lb block and of the ub block
+__global__ void __launch_bounds__(256) gw_scan_coop_kernel(GwIndexView ix, u64* const* slabs, const uint32_t* slots, uint32_t n_tasks) {
+    const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t task = gtid >> 2;
+    const int q = (int)(gtid & 3u);
+    if (task >= n_tasks) return;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t gbase = lane & ~3u;
+    const uint32_t gmask = 0xFu << gbase;
+    const uint32_t slot = slots ? slots[task >> 1] : (task >> 1);
+    const int strand = (int)(task & 1u);
+    GwReadCtx* c = reinterpret_cast<GwReadCtx*>(slabs[slot]);
+    if (c->phase == GW_PH_DONE) return;
+    const int m = c->m;
+    const int fm = strand == 0 ? 1 : 0;
+    const GwOccBlock* occ = ix.occ[fm];
+    const uint32_t N = ix.N;
+    const uint32_t C0 = ix.C[fm][0], C1 = ix.C[fm][1], C2 = ix.C[fm][2], C3 = ix.C[fm][3];
+    uint32_t lb = 0, ub = N;
+    int numMismatches = 0, mark = 0, ls = 0, le = 0;
+    bool hasLongest = false;
+    u64 wlo = 0, whi = 0;
+    for (int i = 0; i < m; ++i) {
+        if ((i & 63) == 0) { wlo = c->qlo[strand][i >> 6]; whi = c->qhi[strand][i >> 6]; }
+        const int ch = (int)(((whi & 1ULL) << 1) | (wlo & 1ULL));
+        wlo >>= 1; whi >>= 1;
+        const uint32_t l = lb > N ? N : lb, u = ub > N ? N : ub;
+        const GwU4 ql = gw_ld128(&occ[l >> 7].q[q]);
+        const GwU4 qu = gw_ld128(&occ[u >> 7].q[q]);
+        uint32_t packed = gw_quarter_count1(ql, gw_quarter_mask(l & 127u, q), ch) | (gw_quarter_count1(qu, gw_quarter_mask(u & 127u, q), ch) << 16);
+        packed += __shfl_xor_sync(gmask, packed, 1);
+        packed += __shfl_xor_sync(gmask, packed, 2);
+        const uint32_t cl = __shfl_sync(gmask, ql.x, gbase + ch);
+        const uint32_t cu = __shfl_sync(gmask, qu.x, gbase + ch);
+        const uint32_t Cc = ch == 0 ? C0 : ch == 1 ? C1 : ch == 2 ? C2 : C3;
+        lb = Cc + cl + (packed & 0xFFFFu);
+        ub = Cc + cu + (packed >> 16);
+        if (lb >= ub) {
+            ++numMismatches;
+            if (!hasLongest || (le - ls) < (i - mark)) { hasLongest = true; ls = mark; le = i; }
+            lb = 0; ub = N;
+            mark = i + 1;
+        }
+    }
+    if (!hasLongest || (le - ls) < (m - mark)) { ls = mark; le = m; }
+    if (q == 0) {
+        c->scan_mm[strand] = numMismatches; c->scan_ls[strand] = ls; c->scan_le[strand] = le;
+        c->scan_lb[strand] = lb; c->scan_ub[strand] = ub;
+        atomicAdd(&c->occ_scan, 2u * (uint32_t)m);
+    }
+}
+
+__global__ void gw_search_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active, GwRoundQueues rq) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_active) return;
+    uint32_t slot = active ? active[i] : i;
+    GwSlab s(slabs[slot]);
+    gw_run_read(env, s, slot, rq);
+}
+
+__global__ void gw_locate_kernel(GwIndexView ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t id = req[i];
+    gw_locate_req(ix, slabs[id >> 1], id & 1u);
+}
+
+__global__ void gw_verify_kernel(GwIndexView ix, u64* const* slabs, const uint32_t* req, uint32_t n, int band_k, GwU64x2* hist) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t id = req[i];
+    gw_verify_req(ix, slabs[id >> 1], id & 1u, band_k, hist + i, (size_t)n);
+}
+
+// collects the slots whose slab overflowed (rerun with the large slab)
+__global__ void gw_collect_overflow_kernel(u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const GwReadCtx* c = reinterpret_cast<const GwReadCtx*>(slabs[i]);
+    if (c->status == GW_ST_OVERFLOW) list[atomicAdd(count, 1u)] = i;
+}
+
+__global__ void gw_emit_count_kernel(u64* const* slabs, uint32_t n, GwDevConfig cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long v[7] = {0, 0, 0, 0, 0, 0, 0};
+    if (i < n) {
+        gw_emit_count(slabs[i], cfg, &n_rec[i], &n_cig[i]);
+        const GwReadCtx* c = reinterpret_cast<const GwReadCtx*>(slabs[i]);
+        v[0] = (unsigned long long)c->n_fm; v[1] = (unsigned long long)c->n_sw; v[2] = (unsigned long long)c->n_cut; v[3] = (unsigned long long)c->n_filt;
+        v[4] = c->occ_scan; v[5] = c->occ_search; v[6] = c->occ_locate;
+    }
+#pragma unroll
+    for (int j = 0; j < 7; ++j) {
+        unsigned long long x = v[j];
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xFFFFFFFFu, x, o);
+        if ((threadIdx.x & 31u) == 0 && x) atomicAdd(&totals[j], x);
+    }
+}
+
+// single-block exclusive scan of two u32 arrays into u64 offsets (+ base); totals to out_tot[0..1]
+__global__ void gw_scan2_kernel(const uint32_t* a, const uint32_t* b, uint32_t n, unsigned long long base_a, unsigned long long base_b,
+                                unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot) {
+    __shared__ unsigned long long sa[1024], sb[1024];
+    const uint32_t t = threadIdx.x, T = blockDim.x;
+    const uint32_t per = (n + T - 1) / T;
+    const uint32_t lo = min(n, t * per), hi = min(n, lo + per);
+    unsigned long long xa = 0, xb = 0;
+    for (uint32_t i = lo; i < hi; ++i) { xa += a[i]; xb += b[i]; }
+    sa[t] = xa; sb[t] = xb;
+    __syncthreads();
+    for (uint32_t d = 1; d < T; d <<= 1) {
+        unsigned long long ya = t >= d ? sa[t - d] : 0, yb = t >= d ? sb[t - d] : 0;
+        __syncthreads();
+        sa[t] += ya; sb[t] += yb;
+        __syncthreads();
+    }
+    unsigned long long pa = base_a + sa[t] - xa, pb = base_b + sb[t] - xb;
+    for (uint32_t i = lo; i < hi; ++i) { oa[i] = pa; ob[i] = pb; pa += a[i]; pb += b[i]; }
+    if (t == T - 1) { out_tot[0] = sa[t]; out_tot[1] = sb[t]; }
+}
+
+__global__ void gw_emit_write_kernel(u64* const* slabs, uint32_t n, GwDevConfig cfg, uint32_t read_base, const unsigned long long* rec_off,
+                                     const unsigned long long* cig_off, GwHitRec* recs, unsigned long long rec_cap, uint32_t* cigs,
+                                     unsigned long long cig_cap) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    gw_emit_write(slabs[i], cfg, read_base + i, recs, rec_off[i], rec_cap, cigs, cig_off[i], cig_cap);
+}
+
+__global__ void gw_fill_slab_ptrs_kernel(u64** slabs, u64* base, size_t slab_words, const uint32_t* slots, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t slot = slots ? slots[i] : i;
+    slabs[slot] = base + (size_t)i * slab_words;
+}
+
+// ---- component kernels (parity tests of single reference methods) ------------------------------------------
+__global__ void gw_rank_acgtn_kernel(GwIndexView ix, int which, const uint32_t* pos, uint32_t n, uint32_t* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t p = gw_clampN(ix, pos[i]);
+    GwBlk b = gw_load_block(ix.occ[which] + (p >> 7));
+    uint32_t r[4];
+    gw_rank4(b, p & 127u, r);
+    out[i * 5 + 0] = r[0]; out[i * 5 + 1] = r[1]; out[i * 5 + 2] = r[2]; out[i * 5 + 3] = r[3];
+    out[i * 5 + 4] = gw_rankN(b, p & ~127u, p & 127u);
+}
+
+__global__ void gw_locate_rows_kernel(GwIndexView ix, int which, const uint32_t* rows, uint32_t n, uint32_t* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t steps;
+    out[i] = gw_sa_get(ix, which, rows[i], &steps);
+}
+
+__global__ void gw_scan_export_kernel(u64* const* slabs, uint32_t n, int strand, uint32_t* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const GwReadCtx* c = reinterpret_cast<const GwReadCtx*>(slabs[i]);
+    out[i * 5 + 0] = (uint32_t)c->scan_mm[strand]; out[i * 5 + 1] = (uint32_t)c->scan_ls[strand]; out[i * 5 + 2] = (uint32_t)c->scan_le[strand];
+    out[i * 5 + 3] = c->scan_lb[strand]; out[i * 5 + 4] = c->scan_ub[strand];
+}
+
+// alignBlockDetailed over explicit (ref, query) ASCII pairs
+__global__ void gw_verify_pairs_kernel(const char* refs, const u64* ref_off, const char* queries, const u64* query_off, uint32_t n, int band_k,
+                                       int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride, GwU64x2* hist, uint32_t max_m) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const char* r = refs + ref_off[i];
+    const char* qs = queries + query_off[i];
+    const int Ncols = (int)(ref_off[i + 1] - ref_off[i]);
+    const int m = (int)(query_off[i + 1] - query_off[i]);
+    auto qsym = [&](int j) -> int { return gw_code_of((unsigned char)qs[j]); };
+    auto refsym = [&](int j) -> int { return gw_code_of((unsigned char)r[j]); };
+    u64 peq[4][GW_MAX_NB];
+    for (int a = 0; a < 4; ++a) for (int b = 0; b < GW_MAX_NB; ++b) peq[a][b] = 0;
+    for (int j = 0; j < m; ++j) {
+        int cde = qsym(j);
+        if (cde == 4) { for (int a = 0; a < 4; ++a) peq[a][j >> 6] |= 1ULL << (j & 63); }  // QueryMask.java:50-55: N matches every base
+        else peq[cde][j >> 6] |= 1ULL << (j & 63);
+    }
+    uint32_t cig[GW_CIG_CAP];
+    GwVerifyOut out;
+    gw_verify(m, Ncols, band_k, peq, refsym, qsym, hist + i, (size_t)n, cig, &out);
+    result[i * 4 + 0] = out.valid; result[i * 4 + 1] = out.pos; result[i * 4 + 2] = out.diff;
+    result[i * 4 + 3] = out.cig_overflow ? -1 : out.cig_n;
+    for (int j = 0; j < out.cig_n && j < (int)cigar_stride; ++j) cigar_ops[(size_t)i * cigar_stride + j] = cig[j];
+}
+
+// ---------------------------------------------------------------------------------------------------------
+static inline unsigned gw_grid(uint64_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
+
+
+void gwk_fill_slab_ptrs(cudaStream_t st, u64** slabs, u64* base, size_t slab_words, const uint32_t* slots, uint32_t n) {
+    if (n) gw_fill_slab_ptrs_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, base, slab_words, slots, n);
+}
+void gwk_prep(cudaStream_t st, const GwBatchView& bv, u64* const* slabs, const uint32_t* slots, uint32_t n, uint32_t read_base, const GwSlabParams& sp) {
+    if (n) gw_prep_kernel<<<gw_grid(n, 128), 128, 0, st>>>(bv, slabs, slots, n, read_base, sp);
+}
+void gwk_scan(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* slots, uint32_t n_slots, int coop) {
+    if (!n_slots) return;
+    const uint64_t n_tasks = 2ull * n_slots;
+    if (coop) gw_scan_coop_kernel<<<gw_grid(n_tasks * 4, 256), 256, 0, st>>>(ix, slabs, slots, (uint32_t)n_tasks);
+    else gw_scan_kernel<<<gw_grid(n_tasks, 128), 128, 0, st>>>(ix, slabs, slots, (uint32_t)n_tasks);
+}
+void gwk_search(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, const GwRoundQueues& rq) {
+    if (n_active) gw_search_kernel<<<gw_grid(n_active, 64), 64, 0, st>>>(env, slabs, active, n_active, rq);
+}
+void gwk_locate(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
+    if (n) gw_locate_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, slabs, req, n);
+}
+void gwk_verify(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n, int band_k, void* hist) {
+    if (n) gw_verify_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, slabs, req, n, band_k, (GwU64x2*)hist);
+}
+void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count) {
+    if (n) gw_collect_overflow_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, list, count);
+}
+void gwk_emit_count(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals) {
+    if (n) gw_emit_count_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, cfg, n_rec, n_cig, totals);
+}
+void gwk_scan2(cudaStream_t st, const uint32_t* a, const uint32_t* b, uint32_t n, unsigned long long base_a, unsigned long long base_b,
+               unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot) {
+    gw_scan2_kernel<<<1, 1024, 0, st>>>(a, b, n, base_a, base_b, oa, ob, out_tot);
+}
+void gwk_emit_write(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t read_base, const unsigned long long* rec_off,
+                    const unsigned long long* cig_off, void* recs, unsigned long long rec_cap, uint32_t* cigs, unsigned long long cig_cap) {
+    if (n) gw_emit_write_kernel<<<gw_grid(n, 128), 128, 0, st>>>(slabs, n, cfg, read_base, rec_off, cig_off, (GwHitRec*)recs, rec_cap, cigs, cig_cap);
+}
+void gwk_rank_acgtn(cudaStream_t st, const GwIndexView& ix, int which, const uint32_t* pos, uint32_t n, uint32_t* out) {
+    if (n) gw_rank_acgtn_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, which, pos, n, out);
+}
+void gwk_locate_rows(cudaStream_t st, const GwIndexView& ix, int which, const uint32_t* rows, uint32_t n, uint32_t* out) {
+    if (n) gw_locate_rows_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, which, rows, n, out);
+}
+void gwk_scan_export(cudaStream_t st, u64* const* slabs, uint32_t n, int strand, uint32_t* out) {
+    if (n) gw_scan_export_kernel<<<gw_grid(n, 128), 128, 0, st>>>(slabs, n, strand, out);
+}
+void gwk_verify_pairs(cudaStream_t st, const char* refs, const u64* ref_off, const char* queries, const u64* query_off, uint32_t n, int band_k,
+                      int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride, void* hist, uint32_t max_m) {
+    if (n) gw_verify_pairs_kernel<<<gw_grid(n, 128), 128, 0, st>>>(refs, ref_off, queries, query_off, n, band_k, result, cigar_ops, cigar_stride, (GwU64x2*)hist, max_m);
+}

@@ -1,0 +1,23 @@
+// gw_kernels.h — host-callable launchers of the kernels in gw_kernels.cu (all asynchronous on the given stream).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "gw_bodies.cuh"
+
+void gwk_fill_slab_ptrs(cudaStream_t st, u64** slabs, u64* base, size_t slab_words, const uint32_t* slots, uint32_t n);
+void gwk_prep(cudaStream_t st, const GwBatchView& bv, u64* const* slabs, const uint32_t* slots, uint32_t n, uint32_t read_base, const GwSlabParams& sp);
+void gwk_scan(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* slots, uint32_t n_slots, int coop);
+void gwk_search(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, const GwRoundQueues& rq);
+void gwk_locate(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n);
+void gwk_verify(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n, int band_k, void* hist);
+void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count);
+void gwk_emit_count(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals);
+void gwk_scan2(cudaStream_t st, const uint32_t* a, const uint32_t* b, uint32_t n, unsigned long long base_a, unsigned long long base_b,
+               unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot);
+void gwk_emit_write(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t read_base, const unsigned long long* rec_off,
+                    const unsigned long long* cig_off, void* recs, unsigned long long rec_cap, uint32_t* cigs, unsigned long long cig_cap);
+void gwk_rank_acgtn(cudaStream_t st, const GwIndexView& ix, int which, const uint32_t* pos, uint32_t n, uint32_t* out);
+void gwk_locate_rows(cudaStream_t st, const GwIndexView& ix, int which, const uint32_t* rows, uint32_t n, uint32_t* out);
+void gwk_scan_export(cudaStream_t st, u64* const* slabs, uint32_t n, int strand, uint32_t* out);
+void gwk_verify_pairs(cudaStream_t st, const char* refs, const u64* ref_off, const char* queries, const u64* query_off, uint32_t n, int band_k,
+                      int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride, void* hist, uint32_t max_m);

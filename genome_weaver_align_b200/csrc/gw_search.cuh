@@ -18,20 +18,16 @@ struct GwSearchEnv {
     GwStaircaseView sf;
 };
 
-#define GW_ST_OK 0
-#define GW_ST_ABORT 2
-#define GW_ST_UNSUPPORTED 3
-#define GW_ST_OVERFLOW 100   // internal: slab too small, rerun in the large-slab pass
 
-__device__ __forceinline__ GwState* gw_st(const GwSlab& s, int32_t off) { return reinterpret_cast<GwState*>(s.at(off)); }
+GW_HD GwState* gw_st(const GwSlab& s, int32_t off) { return reinterpret_cast<GwState*>(s.at(off)); }
 
 // SearchState.getNumSplit / score / upperBoundOfScore
-__device__ __forceinline__ int gw_num_split(const GwSlab& s, const GwState* st) {
+GW_HD int gw_num_split(const GwSlab& s, const GwState* st) {
     int n = 0;
     for (int32_t o = st->next_split; o >= 0; o = gw_st(s, o)->next_split) ++n;
     return n;
 }
-__device__ __forceinline__ int gw_score(const GwSlab& s, const GwDevConfig& cfg, const GwState* st, bool upper) {
+GW_HD int gw_score(const GwSlab& s, const GwDevConfig& cfg, const GwState* st, bool upper) {
     int total = 0;
     int nsplit = gw_num_split(s, st);
     for (const GwState* p = st;;) {
@@ -45,7 +41,7 @@ __device__ __forceinline__ int gw_score(const GwSlab& s, const GwDevConfig& cfg,
     return total;
 }
 // StateQueue comparator
-__device__ __forceinline__ int gw_compare(const GwSlab& s, const GwDevConfig& cfg, int32_t a, int32_t b) {
+GW_HD int gw_compare(const GwSlab& s, const GwDevConfig& cfg, int32_t a, int32_t b) {
     const GwState* o1 = gw_st(s, a);
     const GwState* o2 = gw_st(s, b);
     int diff = gw_priority(o1) - gw_priority(o2);
@@ -54,7 +50,7 @@ __device__ __forceinline__ int gw_compare(const GwSlab& s, const GwDevConfig& cf
     return diff;
 }
 // java.util.PriorityQueue.offer (siftUp) ; returns false on capacity overflow
-__device__ __forceinline__ bool gw_queue_add(const GwSlab& s, const GwDevConfig& cfg, int32_t e) {
+GW_HD bool gw_queue_add(const GwSlab& s, const GwDevConfig& cfg, int32_t e) {
     if (e < 0) return true;  // StateQueue.add(null) is a no-op
     GwReadCtx* c = s.ctx();
     int32_t* q = s.queue();
@@ -72,7 +68,7 @@ __device__ __forceinline__ bool gw_queue_add(const GwSlab& s, const GwDevConfig&
     return true;
 }
 // java.util.PriorityQueue.poll (siftDown)
-__device__ __forceinline__ int32_t gw_queue_poll(const GwSlab& s, const GwDevConfig& cfg) {
+GW_HD int32_t gw_queue_poll(const GwSlab& s, const GwDevConfig& cfg) {
     GwReadCtx* c = s.ctx();
     int32_t* q = s.queue();
     int n = --c->qn;
@@ -95,11 +91,11 @@ __device__ __forceinline__ int32_t gw_queue_poll(const GwSlab& s, const GwDevCon
 }
 
 // allocate a state with `height` NFA rows; fields are filled by the caller
-__device__ __forceinline__ int32_t gw_alloc_state(const GwSlab& s, int height) {
+GW_HD int32_t gw_alloc_state(const GwSlab& s, int height) {
     return gw_alloc(s, GW_STATE_WORDS + (uint32_t)height);
 }
 
-__device__ __forceinline__ void gw_set_init_siset(const GwIndexView& ix, GwState* st, int dir) {
+GW_HD void gw_set_init_siset(const GwIndexView& ix, GwState* st, int dir) {
     st->f_valid = st->b_valid = 0;
     if (dir == GW_DIR_F || dir == GW_DIR_BF) {
         st->f_valid = (uint8_t)ix.init_valid;
@@ -113,7 +109,7 @@ __device__ __forceinline__ void gw_set_init_siset(const GwIndexView& ix, GwState
 }
 
 // SearchState(k, null, cursor, priority): initial state with diagonal NFA (:753-757)
-__device__ __forceinline__ int32_t gw_initial_state(const GwSearchEnv& env, const GwSlab& s, int strand, int dir, int start, int end,
+GW_HD int32_t gw_initial_state(const GwSearchEnv& env, const GwSlab& s, int strand, int dir, int start, int end,
                                                     int cursor, int pivot, int k, int minK, int priority) {
     int32_t off = gw_alloc_state(s, k + 1);
     if (off < 0) return -1;
@@ -130,7 +126,7 @@ __device__ __forceinline__ int32_t gw_initial_state(const GwSearchEnv& env, cons
     return off;
 }
 
-__device__ __forceinline__ bool gw_si_is_empty(const GwState* c, int ch) {
+GW_HD bool gw_si_is_empty(const GwState* c, int ch) {
     if (c->si_kind == GW_SI_EMPTY || c->si_kind == GW_SI_NULL) return true;
     if (c->si_kind == GW_SI_B) return !((c->b_valid >> ch) & 1) || c->sib[ch][0] >= c->sib[ch][1];
     return !((c->f_valid >> ch) & 1) || c->sif[ch][0] >= c->sif[ch][1];
@@ -142,7 +138,7 @@ struct GwSiSet {
 };
 
 // Cursor.nextSi + FMIndexOnGenome.bidirectionalSearch: two rank queries on one index
-__device__ __forceinline__ void gw_next_si(const GwIndexView& ix, const GwState* c, int ch, GwSiSet* out, uint32_t* occ_lookups) {
+GW_HD void gw_next_si(const GwIndexView& ix, const GwState* c, int ch, GwSiSet* out, uint32_t* occ_lookups) {
     bool hasF = (c->si_kind == GW_SI_F || c->si_kind == GW_SI_BD) && ((c->f_valid >> ch) & 1);
     bool hasB = (c->si_kind == GW_SI_B || c->si_kind == GW_SI_BD) && ((c->b_valid >> ch) & 1);
     if (gw_dir(c) == GW_DIR_BF && c->cursor >= c->end - 1) hasF = false;
@@ -153,10 +149,10 @@ __device__ __forceinline__ void gw_next_si(const GwIndexView& ix, const GwState*
     const uint32_t lb = gw_clampN(ix, hasF ? c->sif[ch][0] : c->sib[ch][0]);
     const uint32_t ub = gw_clampN(ix, hasF ? c->sif[ch][1] : c->sib[ch][1]);
     uint32_t lo[4], hi[4];
-    GwBlockRegs bl = gw_load_block(ix.occ[fm] + (lb >> 7));
+    GwBlk bl = gw_load_block(ix.occ[fm] + (lb >> 7));
     gw_rank4(bl, lb & 127u, lo);
     if ((ub >> 7) == (lb >> 7)) gw_rank4(bl, ub & 127u, hi);  // same 64 B line: one load serves both queries
-    else { GwBlockRegs bu = gw_load_block(ix.occ[fm] + (ub >> 7)); gw_rank4(bu, ub & 127u, hi); }
+    else { GwBlk bu = gw_load_block(ix.occ[fm] + (ub >> 7)); gw_rank4(bu, ub & 127u, hi); }
     *occ_lookups += 2;
     uint32_t (*dst)[2] = hasF ? out->sif : out->sib;
     uint8_t valid = 0;
@@ -185,7 +181,7 @@ __device__ __forceinline__ void gw_next_si(const GwIndexView& ix, const GwState*
 
 // ReadAlignmentNFA.nextState + SearchState.nextState: returns arena offset of the new state, -1 for "no match" (null),
 // -2 on slab overflow
-__device__ __forceinline__ int32_t gw_next_state(const GwSearchEnv& env, const GwSlab& s, int32_t c_off, int ch, const GwSiSet& nextSi,
+GW_HD int32_t gw_next_state(const GwSearchEnv& env, const GwSlab& s, int32_t c_off, int ch, const GwSiSet& nextSi,
                                                  const u64* sf_tbl, int sf_kk) {
     GwReadCtx* ctx = s.ctx();
     GwState* c = gw_st(s, c_off);
@@ -259,7 +255,7 @@ __device__ __forceinline__ int32_t gw_next_state(const GwSearchEnv& env, const G
 }
 
 // SearchState.nextStateAfterSplit (clip == false) / nextStateAfterClipping (clip == true); -1 null, -2 overflow, -3 abort
-__device__ __forceinline__ int32_t gw_split_state(const GwSearchEnv& env, const GwSlab& s, int32_t c_off, int k, bool clip) {
+GW_HD int32_t gw_split_state(const GwSearchEnv& env, const GwSlab& s, int32_t c_off, int k, bool clip) {
     GwState* c = gw_st(s, c_off);
     c->state |= 1 << 4;
     const int minK = gw_lower_k(c);
@@ -309,7 +305,7 @@ __device__ __forceinline__ int32_t gw_split_state(const GwSearchEnv& env, const 
 }
 
 // SearchState.update(oldState, newState) on baseState: returns the queue entry (or -1 for null)
-__device__ __forceinline__ int32_t gw_update(const GwSlab& s, int32_t base, int32_t oldState, int32_t newState) {
+GW_HD int32_t gw_update(const GwSlab& s, int32_t base, int32_t oldState, int32_t newState) {
     if (oldState == base) return newState;
     int32_t prev = base;
     while (gw_st(s, prev)->next_split != oldState) {
@@ -321,18 +317,18 @@ __device__ __forceinline__ int32_t gw_update(const GwSlab& s, int32_t base, int3
 }
 
 // ---- hit list -----------------------------------------------------------------------------------------
-__device__ __forceinline__ GwHitNode* gw_hit(const GwSlab& s, int32_t off) { return reinterpret_cast<GwHitNode*>(s.at(off)); }
-__device__ __forceinline__ int gw_hit_total_match(const GwSlab& s, const GwHitNode* h) {
+GW_HD GwHitNode* gw_hit(const GwSlab& s, int32_t off) { return reinterpret_cast<GwHitNode*>(s.at(off)); }
+GW_HD int gw_hit_total_match(const GwSlab& s, const GwHitNode* h) {
     int t = 0;
     for (;;) { t += h->match_length; if (h->next_split < 0) break; h = gw_hit(s, h->next_split); }
     return t;
 }
-__device__ __forceinline__ int gw_hit_total_diff(const GwSlab& s, const GwHitNode* h) {
+GW_HD int gw_hit_total_diff(const GwSlab& s, const GwHitNode* h) {
     int t = 0;
     for (;;) { t += h->diff; if (h->next_split < 0) break; t += 1; h = gw_hit(s, h->next_split); }
     return t;
 }
-__device__ __forceinline__ int gw_hit_total_score(const GwSlab& s, const GwDevConfig& cfg, const GwHitNode* h) {
+GW_HD int gw_hit_total_score(const GwSlab& s, const GwDevConfig& cfg, const GwHitNode* h) {
     int t = 0;
     for (;;) {
         t += h->match_length * cfg.match_score - h->diff * cfg.mismatch_penalty;
@@ -342,7 +338,7 @@ __device__ __forceinline__ int gw_hit_total_score(const GwSlab& s, const GwDevCo
     }
     return t;
 }
-__device__ __forceinline__ int32_t gw_new_hit(const GwSlab& s, int chr, int pos, int matchLength, int qStart, int qEnd, int diff, int strand,
+GW_HD int32_t gw_new_hit(const GwSlab& s, int chr, int pos, int matchLength, int qStart, int qEnd, int diff, int strand,
                                               const uint32_t* cig, int cigN, int numHits) {
     int32_t off = gw_alloc(s, GW_HIT_WORDS + (uint32_t)((cigN + 1) / 2));
     if (off < 0) return -1;
@@ -354,7 +350,7 @@ __device__ __forceinline__ int32_t gw_new_hit(const GwSlab& s, int chr, int pos,
     return off;
 }
 // AlignmentResultHolder.add ; false on hit-list overflow
-__device__ __forceinline__ bool gw_add_result(const GwSlab& s, const GwDevConfig& cfg, int32_t hit) {
+GW_HD bool gw_add_result(const GwSlab& s, const GwDevConfig& cfg, int32_t hit) {
     GwReadCtx* c = s.ctx();
     const GwHitNode* h = gw_hit(s, hit);
     int newK = gw_hit_total_diff(s, h), matchLen = gw_hit_total_match(s, h), newScore = gw_hit_total_score(s, cfg, h);

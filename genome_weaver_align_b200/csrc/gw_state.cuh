@@ -33,7 +33,9 @@ struct GwReadCtx {
     int32_t scan_mm[2], scan_ls[2], scan_le[2];
     uint32_t scan_lb[2], scan_ub[2];
     int32_t pend_base, pend_n;
-    int32_t count_n, pad0;
+    int32_t count_n, read_id;
+    GwSlabParams sp;          // geometry of the slab this context lives in
+    uint32_t occ_scan, occ_search, occ_locate;   // occurrence-table lookups done for this read (roofline work unit)
     GwPendFrag pend[2];
     u64 qlo[2][GW_MAX_NB], qhi[2][GW_MAX_NB];  // q[0] = read, q[1] = its complement, N replaced by A in both
 };
@@ -44,15 +46,18 @@ struct GwReadCtx {
 struct GwSlab {
     u64* base;
     GwSlabParams sp;
-    __device__ __forceinline__ GwReadCtx* ctx() const { return reinterpret_cast<GwReadCtx*>(base); }
-    __device__ __forceinline__ u64* masks() const { return base + GW_CTX_WORDS; }
-    __device__ __forceinline__ int32_t* queue() const { return reinterpret_cast<int32_t*>(base + GW_CTX_WORDS + GW_MASK_WORDS); }
-    __device__ __forceinline__ int32_t* hits() const { return queue() + sp.queue_cap; }
-    __device__ __forceinline__ uint32_t arena_begin() const { return GW_CTX_WORDS + GW_MASK_WORDS + (sp.queue_cap + sp.hit_cap + 1) / 2; }
-    __device__ __forceinline__ u64* at(int32_t off) const { return base + off; }
+    GW_HD GwSlab() : base(nullptr) {}
+    GW_HD explicit GwSlab(u64* b) : base(b) { sp = reinterpret_cast<GwReadCtx*>(b)->sp; }
+    GW_HD GwSlab(u64* b, const GwSlabParams& p) : base(b), sp(p) {}
+    GW_HD GwReadCtx* ctx() const { return reinterpret_cast<GwReadCtx*>(base); }
+    GW_HD u64* masks() const { return base + GW_CTX_WORDS; }
+    GW_HD int32_t* queue() const { return reinterpret_cast<int32_t*>(base + GW_CTX_WORDS + GW_MASK_WORDS); }
+    GW_HD int32_t* hits() const { return queue() + sp.queue_cap; }
+    GW_HD uint32_t arena_begin() const { return GW_CTX_WORDS + GW_MASK_WORDS + (sp.queue_cap + sp.hit_cap + 1) / 2; }
+    GW_HD u64* at(int32_t off) const { return base + off; }
 };
 
-__device__ __forceinline__ u64* gw_mask_ptr(const GwSlab& s, int strand, int rev, int ch) {
+GW_HD u64* gw_mask_ptr(const GwSlab& s, int strand, int rev, int ch) {
     return s.masks() + (((strand * 2 + rev) * 4 + ch) * GW_MAX_NB);
 }
 
@@ -85,27 +90,27 @@ struct GwState {
 };
 #define GW_STATE_WORDS ((uint32_t)((sizeof(GwState) + 7) / 8))
 
-__device__ __forceinline__ u64* gw_rows(GwState* s) { return reinterpret_cast<u64*>(s) + GW_STATE_WORDS; }
-__device__ __forceinline__ int gw_strand(const GwState* s) { return s->cflag & 1; }
-__device__ __forceinline__ int gw_dir(const GwState* s) { int d = (s->cflag >> 1) & 3; return d == 3 ? GW_DIR_F : d; }
-__device__ __forceinline__ bool gw_is_fwd(const GwState* s) { return gw_dir(s) != GW_DIR_B; }
-__device__ __forceinline__ int gw_frag_len(const GwState* s) { return s->end - s->start; }
-__device__ __forceinline__ int gw_processed(const GwState* s) { return gw_is_fwd(s) ? s->cursor - s->pivot : s->end - s->cursor; }
-__device__ __forceinline__ int gw_remaining(const GwState* s) { return gw_frag_len(s) - gw_processed(s); }
-__device__ __forceinline__ int gw_next_index(const GwState* s) { return gw_is_fwd(s) ? s->cursor : s->cursor - 1; }
-__device__ __forceinline__ int gw_head_offset(const GwState* s) {
+GW_HD u64* gw_rows(GwState* s) { return reinterpret_cast<u64*>(s) + GW_STATE_WORDS; }
+GW_HD int gw_strand(const GwState* s) { return s->cflag & 1; }
+GW_HD int gw_dir(const GwState* s) { int d = (s->cflag >> 1) & 3; return d == 3 ? GW_DIR_F : d; }
+GW_HD bool gw_is_fwd(const GwState* s) { return gw_dir(s) != GW_DIR_B; }
+GW_HD int gw_frag_len(const GwState* s) { return s->end - s->start; }
+GW_HD int gw_processed(const GwState* s) { return gw_is_fwd(s) ? s->cursor - s->pivot : s->end - s->cursor; }
+GW_HD int gw_remaining(const GwState* s) { return gw_frag_len(s) - gw_processed(s); }
+GW_HD int gw_next_index(const GwState* s) { return gw_is_fwd(s) ? s->cursor : s->cursor - 1; }
+GW_HD int gw_head_offset(const GwState* s) {
     int off = s->cursor - s->start;
     if (gw_strand(s) == 1) off = gw_frag_len(s) - off;
     return off;
 }
-__device__ __forceinline__ int gw_lower_k(const GwState* s) { return ((uint32_t)s->state >> 8) & 0xFF; }
-__device__ __forceinline__ void gw_set_lower_k(GwState* s, int d) { s->state = (s->state & ~(0xFF << 8)) | ((d & 0xFF) << 8); }
-__device__ __forceinline__ int gw_priority(const GwState* s) { return ((uint32_t)s->state >> 16) & 0xFF; }
-__device__ __forceinline__ bool gw_has_hit(const GwState* s) { return (((uint32_t)s->state >> 24) & 1) != 0; }
-__device__ __forceinline__ bool gw_is_clipped(const GwState* s) { return (((uint32_t)s->state >> 25) & 1) != 0; }
-__device__ __forceinline__ bool gw_is_finished(const GwState* s) { return (s->state & 0x1F) == 0x1F; }
-__device__ __forceinline__ int gw_current_acgt(const GwState* s) { int c = (s->state >> 5) & 7; return c > 4 ? 4 : c; }
-__device__ __forceinline__ int gw_pack_state(int ch, int minK, int prio, bool hasMatch) {
+GW_HD int gw_lower_k(const GwState* s) { return ((uint32_t)s->state >> 8) & 0xFF; }
+GW_HD void gw_set_lower_k(GwState* s, int d) { s->state = (s->state & ~(0xFF << 8)) | ((d & 0xFF) << 8); }
+GW_HD int gw_priority(const GwState* s) { return ((uint32_t)s->state >> 16) & 0xFF; }
+GW_HD bool gw_has_hit(const GwState* s) { return (((uint32_t)s->state >> 24) & 1) != 0; }
+GW_HD bool gw_is_clipped(const GwState* s) { return (((uint32_t)s->state >> 25) & 1) != 0; }
+GW_HD bool gw_is_finished(const GwState* s) { return (s->state & 0x1F) == 0x1F; }
+GW_HD int gw_current_acgt(const GwState* s) { int c = (s->state >> 5) & 7; return c > 4 ? 4 : c; }
+GW_HD int gw_pack_state(int ch, int minK, int prio, bool hasMatch) {
     return ((ch & 7) << 5) | ((minK & 0xFF) << 8) | ((prio & 0xFF) << 16) | ((hasMatch ? 1 : 0) << 24);
 }
 
@@ -119,10 +124,10 @@ struct GwHitNode {
     // followed by cig_n u32 cigar elements (BAM encoding)
 };
 #define GW_HIT_WORDS ((uint32_t)((sizeof(GwHitNode) + 7) / 8))
-__device__ __forceinline__ uint32_t* gw_hit_cigar(GwHitNode* h) { return reinterpret_cast<uint32_t*>(reinterpret_cast<u64*>(h) + GW_HIT_WORDS); }
+GW_HD uint32_t* gw_hit_cigar(GwHitNode* h) { return reinterpret_cast<uint32_t*>(reinterpret_cast<u64*>(h) + GW_HIT_WORDS); }
 
 // bump allocation; returns -1 (and flags the read for the large-slab pass) on overflow
-__device__ __forceinline__ int32_t gw_alloc(const GwSlab& s, uint32_t words) {
+GW_HD int32_t gw_alloc(const GwSlab& s, uint32_t words) {
     GwReadCtx* c = s.ctx();
     uint32_t top = (uint32_t)c->top;
     if (top + words > s.sp.slab_words) return -1;
@@ -131,7 +136,7 @@ __device__ __forceinline__ int32_t gw_alloc(const GwSlab& s, uint32_t words) {
 }
 
 // ---- BitVector.substring64 over nb blocks -----------------------------------------------------------------
-__device__ __forceinline__ u64 gw_substring64(const u64* block, int nb, int start, int end) {
+GW_HD u64 gw_substring64(const u64* block, int nb, int start, int end) {
     int pos = start / 64;
     if (pos >= nb) return 0ULL;
     int range = end - start;
@@ -143,7 +148,7 @@ __device__ __forceinline__ u64 gw_substring64(const u64* block, int nb, int star
 }
 
 // QueryMask.getBidirectionalPatternMask64
-__device__ __forceinline__ u64 gw_pattern_mask64(const GwSlab& s, int strand, int m, bool dirIsForward, int nextIdx, int pivot,
+GW_HD u64 gw_pattern_mask64(const GwSlab& s, int strand, int m, bool dirIsForward, int nextIdx, int pivot,
                                                  int cursor, int ch, int margin) {
     const int nb = (m + 63) >> 6;
     u64 p;
@@ -163,7 +168,7 @@ __device__ __forceinline__ u64 gw_pattern_mask64(const GwSlab& s, int strand, in
 }
 
 // StaircaseFilter.getStairCaseMask64bit for the filter (m, kk); tbl points at the (kk+1) x nb words of that filter
-__device__ __forceinline__ u64 gw_staircase64(const u64* tbl, int m, int kk, int row, int offset) {
+GW_HD u64 gw_staircase64(const u64* tbl, int m, int kk, int row, int offset) {
     if (row >= kk + 1) return 0ULL;
     const int nb = (m + 63) >> 6;
     const u64* bv = tbl + row * nb;

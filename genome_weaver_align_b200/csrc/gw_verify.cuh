@@ -14,37 +14,33 @@ struct GwVerifyOut {
     bool cig_overflow;
 };
 
-#define GW_OP_M 0u
-#define GW_OP_I 1u
-#define GW_OP_D 2u
-#define GW_OP_S 4u
 
-// hist: scratch base for this request; element (col, blk) at hist[((col * bMax + blk) * stride)] as ulonglong2 (vp, vn)
+// hist: scratch base for this request; element (col, blk) at hist[((col * bMax + blk) * stride)] as GwU64x2 (vp, vn)
 // peq: [4][bMax] pattern masks of the query (bits >= m clear); refsym(j): reference symbol (0..4) of window column j
 // qsym(i): query symbol (0..4) of row i
 template <typename RefSym, typename QSym>
-__device__ __forceinline__ void gw_verify(int m, int Ncols, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, QSym qsym,
-                                          ulonglong2* hist, size_t stride, uint32_t* cig_out, GwVerifyOut* out) {
+GW_HD void gw_verify(int m, int Ncols, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, QSym qsym,
+                                          GwU64x2* hist, size_t stride, uint32_t* cig_out, GwVerifyOut* out) {
     const int w = 64;
-    const int bMax = max(1, (m + w - 1) / w);
+    const int bMax = gw_max(1, (m + w - 1) / w);
     int D[GW_MAX_NB];
     int scoreBoundary[GW_MAX_NB];
     u64 vp[GW_MAX_NB], vn[GW_MAX_NB];  // column j values of the active blocks
 #pragma unroll
     for (int r = 0; r < GW_MAX_NB; ++r) {
         D[r] = 0; vp[r] = ~0ULL; vn[r] = 0ULL;
-        scoreBoundary[r] = max(m - ((r + 1) * w) + band_k, 0);
+        scoreBoundary[r] = gw_max(m - ((r + 1) * w) + band_k, 0);
     }
     D[0] = m;
-    for (int r = 0; r < bMax; ++r) hist[(size_t)r * stride] = make_ulonglong2(~0ULL, 0ULL);  // column 0
-    int bCeil = max(1, (band_k + w - 1) / w);
+    for (int r = 0; r < bMax; ++r) hist[(size_t)r * stride] = GwU64x2{~0ULL, 0ULL};  // column 0
+    int bCeil = gw_max(1, (band_k + w - 1) / w);
     if (bCeil > bMax) bCeil = bMax;  // band_k <= 64 in practice; keeps indices in range
     bool hasBest = false;
     int bestTail = -1, bestDiff = 0;
     for (int j = 0; j < Ncols; ++j) {
         const int ch = refsym(j);
         int carry = 0;
-        ulonglong2* col = hist + (size_t)(j + 1) * bMax * stride;
+        GwU64x2* col = hist + (size_t)(j + 1) * bMax * stride;
         int computed = bCeil;  // blocks whose column j+1 is written in this step
 #pragma unroll
         for (int r = 0; r < GW_MAX_NB; ++r) {
@@ -60,7 +56,7 @@ __device__ __forceinline__ void gw_verify(int m, int Ncols, int band_k, const u6
                 if (carry > 0) hp2 |= 1ULL;
                 vp[r] = hn2 | ~(d0 | hp2);
                 vn[r] = d0 & hp2;
-                col[(size_t)r * stride] = make_ulonglong2(vp[r], vn[r]);
+                col[(size_t)r * stride] = GwU64x2{vp[r], vn[r]};
                 D[r] += hout;
                 carry = hout;
             }
@@ -71,7 +67,7 @@ __device__ __forceinline__ void gw_verify(int m, int Ncols, int band_k, const u6
             u64 x = ch < 4 ? peq[ch][r] : 0ULL;
             if (D[r - 1] - carry <= scoreBoundary[r - 1] && (((x & 1ULL) != 0ULL) | (carry < 0))) {
                 // vp[r][j] = ~0, vn[r][j] = 0 ; then one block step
-                hist[((size_t)j * bMax + r) * stride] = make_ulonglong2(~0ULL, 0ULL);
+                hist[((size_t)j * bMax + r) * stride] = GwU64x2{~0ULL, 0ULL};
                 u64 vpr = ~0ULL, vnr = 0ULL;
                 if (carry < 0) x |= 1ULL;
                 u64 d0 = (((x & vpr) + vpr) ^ vpr) | x | vnr;
@@ -83,7 +79,7 @@ __device__ __forceinline__ void gw_verify(int m, int Ncols, int band_k, const u6
                 if (carry > 0) hp2 |= 1ULL;
                 vp[r] = hn2 | ~(d0 | hp2);
                 vn[r] = d0 & hp2;
-                col[(size_t)r * stride] = make_ulonglong2(vp[r], vn[r]);
+                col[(size_t)r * stride] = GwU64x2{vp[r], vn[r]};
                 D[r] = D[r - 1] - carry + hout;
                 bCeil++;
                 computed = bCeil;
@@ -95,7 +91,7 @@ __device__ __forceinline__ void gw_verify(int m, int Ncols, int band_k, const u6
         }
         // blocks not computed in this step: column j+1 keeps the zero initial value of the Java arrays
         // (a block deactivated just now was computed and keeps its values, as in the reference)
-        for (int r = computed; r < bMax; ++r) col[(size_t)r * stride] = make_ulonglong2(0ULL, 0ULL);
+        for (int r = computed; r < bMax; ++r) col[(size_t)r * stride] = GwU64x2{0ULL, 0ULL};
         if (bCeil == bMax) {
             if (!hasBest) { hasBest = true; bestTail = j; bestDiff = D[bCeil - 1]; }
             else if (bestDiff > D[bCeil - 1]) { bestTail = j; bestDiff = D[bCeil - 1]; }
@@ -114,7 +110,7 @@ __device__ __forceinline__ void gw_verify(int m, int Ncols, int band_k, const u6
         int path = 0;
         if (col >= 0 && row >= 0) {
             int block = row >> 6, offset = row & 63;
-            ulonglong2 v = hist[((size_t)(col + 1) * bMax + block) * stride];
+            GwU64x2 v = hist[((size_t)(col + 1) * bMax + block) * stride];
             bool vpf = (v.x >> offset) & 1ULL, vnf = (v.y >> offset) & 1ULL;
             if (refsym(col) == qsym(row)) path = 1;
             else if (vpf) { path = 3; diff++; }
