@@ -44,5 +44,12 @@ bool gw_staircase_masks(int m, int kk, std::vector<uint64_t>& words);
 // AlignmentScoreConfig.getMaximumEditDistance (AlignmentScoreConfig.java:40-47)
 int gw_max_edit_distance(float k, int read_length);
 
+// ---- index construction on the device (gw_build.cu) --------------------------------------------------------
+// BWT + SA samples (every 32 rows) of the cyclic rotations of codes[0..n); sa_out (optional) receives the full suffix array
+void gw_build_bwt_device(int device, const uint8_t* codes, uint64_t n, std::vector<uint8_t>& bwt, std::vector<uint32_t>& ssa,
+                         std::vector<uint32_t>* sa_out);
+void gw_build_host_index(int device, GwHostIndex& ix);   // fills bwt[2], ssa[2] from text
+
 // ---- SAM formatting (gw_sam.cpp) ---------------------------------------------------------------------------
-struct gw_hit_rec;  // == gw_hit_t
+struct gw_hit_t_tag;
+std::string gw_sam_header_text(const std::vector<GwContig>& ctg);

@@ -125,6 +125,20 @@ int gw_align_batch_device(gw_aligner_t*, const char* d_bases, const uint64_t* d_
  * aligner's stream: [0] prep+quick-scan, [1] search, [2] locate, [3] verify, [4] finalize, [5] whole batch */
 int gw_aligner_last_timing(const gw_aligner_t*, float ms[6]);
 
+/* tunables of an aligner (all optional): "scan_coop" 0/1 (4-lane cooperative quick scan, default 1), "slab_words" (8-byte words of the
+ * per-read work area of the first pass), "big_slab_words" (second pass), "wave_reads" (reads resident per wave) */
+int gw_aligner_set_option(gw_aligner_t*, const char* name, int64_t value);
+
+/* AlignmentRecord.convert + toSAMLine + SAMOutput.emit (align/record/AlignmentRecord.java:92-276, align/SAMOutput.java:72-82) for the hit
+ * records of one batch, on the host. names/quals are concatenated like bases (offset arrays of n_reads+1); quals may be NULL ("*").
+ * *out_len in: capacity of out, out: bytes needed/used (GW_E_CAPACITY when too small). lines_per_read (may be NULL) receives the
+ * number of SAM lines each read produced (0 where convert returns null or the read is outside the reference's domain). */
+int gw_sam_format(const gw_index_t*, const char* names, const uint64_t* name_off, const char* bases, const uint64_t* base_off,
+                  const char* quals, const uint64_t* qual_off, uint32_t n_reads, const gw_hit_t* hits, uint64_t n_hits,
+                  const uint32_t* cigar_ops, char* out, uint64_t* out_len, uint32_t* lines_per_read);
+/* SAMOutput.init: "@SQ\tSN:%s\tLN:%d\n" per contig (align/SAMOutput.java:51-59, align/SequenceBoundary.java:81-87) */
+int gw_sam_header(const gw_index_t*, char* out, uint64_t* out_len);
+
 /* ---- component entry points (used by the parity tests; each replaces one reference method) ---- */
 /* FMIndexOnOccTable.rankACGTN (align/FMIndexOnOccTable.java:53-55) for n positions; which: 0 forward BWT, 1 reverse BWT; out n x 5 */
 int gw_rank_acgtn(const gw_index_t*, int which, const uint32_t* pos, uint32_t n, uint32_t* out);
@@ -139,6 +153,10 @@ int gw_verify_pairs(int device, const char* refs, const uint64_t* ref_off, const
                     int band_k, int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride);
 /* StaircaseFilter(m, kk) masks (align/strategy/StaircaseFilter.java:47-73): (kk+1) x ceil(m/64) words; returns 2 if the reference throws */
 int gw_staircase_table(int m, int kk, uint64_t* out, int cap_words);
+/* CyclicSAIS.SAIS (align/sais/CyclicSAIS.java:223-382): suffix array of the cyclic rotations of an ACGTN string, computed on `device` */
+int gw_cyclic_suffix_array(const char* bases, uint64_t n, int device, uint32_t* sa_out);
+/* AlignmentScoreConfig.getMaximumEditDistance (align/AlignmentScoreConfig.java:40-47) */
+int gw_max_edit_distance_c(float k, int read_length);
 
 #ifdef __cplusplus
 }

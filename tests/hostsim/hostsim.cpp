@@ -1,0 +1,200 @@
+// TEST INFRASTRUCTURE ONLY — host simulator of the device automaton.
+// Compiles the per-thread kernel bodies of genome_weaver_align_b200/csrc (the GW_HD functions in gw_*.cuh) with g++ and
+// runs them sequentially, one "thread" after another, through the same prep / scan / search-locate-verify rounds / emit
+// phases as the CUDA driver in gw_api.cu. It exists so that the automaton logic can be checked against the oracle on a
+// machine without a GPU (`pytest -m "not gpu"`). It is never linked into libgwalign.so and never used by the product:
+// the product path is CUDA only and fails loudly without a device.
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/gw_align.h"
+#include "../../genome_weaver_align_b200/csrc/gw_bodies.cuh"
+#include "../../genome_weaver_align_b200/csrc/gw_host.h"
+#include "../../genome_weaver_align_b200/csrc/gw_image.h"
+
+bool gw_sam_one(const std::vector<GwContig>& ctg, const std::string& name, const char* bases, size_t m, const char* qual, size_t qlen,
+                const gw_hit_t* chain, int n, const uint32_t* ops, std::string& out);
+
+namespace {
+struct SimIndex {
+    GwHostIndex host;
+    GwIndexImage img;
+    GwIndexView view;
+};
+thread_local std::string g_err;
+
+GwSlabParams slab_params(uint32_t words) {   // same rule as gw_api_align.inc
+    GwSlabParams sp;
+    sp.slab_words = words;
+    sp.queue_cap = std::max<uint32_t>(64, std::min<uint32_t>(words / 16, 8192));
+    sp.hit_cap = std::max<uint32_t>(32, std::min<uint32_t>(words / 64, 2048));
+    return sp;
+}
+}  // namespace
+
+extern "C" {
+
+const char* gwsim_last_error() { return g_err.c_str(); }
+
+void* gwsim_open(const char* fasta_path) {
+    try {
+        SimIndex* s = new SimIndex();
+        gw_load_index_files(fasta_path, s->host);
+        gw_layout_index(s->host, s->img);
+        s->view = s->img.view;
+        for (int i = 0; i < 2; ++i) { s->view.occ[i] = s->img.occ[i].data(); s->view.ssa[i] = s->host.ssa[i].data(); }
+        s->view.ref_lo = s->img.ref_lo.data(); s->view.ref_hi = s->img.ref_hi.data(); s->view.ref_nf = s->img.ref_nf.data();
+        s->view.ctg_off = s->img.ctg_off.data(); s->view.ctg_id = s->img.ctg_id.data(); s->view.ctg_rank = s->img.ctg_rank.data();
+        return s;
+    } catch (std::exception& e) { g_err = e.what(); return nullptr; }
+}
+void gwsim_close(void* h) { delete (SimIndex*)h; }
+
+void gwsim_rank_acgtn(void* h, int which, uint32_t pos, uint32_t* out5) {
+    SimIndex* s = (SimIndex*)h;
+    uint32_t p = gw_clampN(s->view, pos);
+    GwBlk b = gw_load_block(s->view.occ[which] + (p >> 7));
+    gw_rank4(b, p & 127u, out5);
+    out5[4] = gw_rankN(b, p & ~127u, p & 127u);
+}
+uint32_t gwsim_locate(void* h, int which, uint32_t row) {
+    uint32_t steps;
+    return gw_sa_get(((SimIndex*)h)->view, which, row, &steps);
+}
+
+// cfg: k, numSplitAllowed, matchScore, mismatchPenalty, splitOpenPenalty, indelEndSkip, bandWidth, reportType, topL
+// returns malloc'ed SAM text; status[n], counters[n*4], lines[n]; *tiers_used = reads that needed a larger work area
+char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bases, const uint64_t* offsets, const char* names,
+                  const uint64_t* name_off, const char* quals, const uint64_t* qual_off, uint32_t slab_words, int* status, int* counters,
+                  int* lines, uint32_t* tiers_used) {
+    try {
+        SimIndex* S = (SimIndex*)h;
+        GwSearchEnv env;
+        env.ix = S->view;
+        env.cfg.k = (float)cfgv[0]; env.cfg.num_split_allowed = (int)cfgv[1]; env.cfg.match_score = (int)cfgv[2];
+        env.cfg.mismatch_penalty = (int)cfgv[3]; env.cfg.split_open_penalty = (int)cfgv[4]; env.cfg.indel_end_skip = (int)cfgv[5];
+        env.cfg.band_width = (int)cfgv[6]; env.cfg.report_type = (int)cfgv[7]; env.cfg.top_l = (int)cfgv[8];
+        // tables (same construction as build_tables in gw_api_align.inc)
+        int32_t k_by_m[GW_MAX_READ_LEN + 1];
+        int kmax = 0;
+        std::vector<u64> words;
+        std::vector<int32_t> base(GW_MAX_READ_LEN + 1, -1);
+        std::vector<uint32_t> abortm(GW_MAX_READ_LEN + 1, 0);
+        for (int m = 0; m <= GW_MAX_READ_LEN; ++m) {
+            int k = m == 0 ? -1 : gw_max_edit_distance(env.cfg.k, m);
+            if (k < 0 || k > GW_MAX_K) k = -1;
+            k_by_m[m] = k;
+            kmax = std::max(kmax, k);
+            if (k < 0) continue;
+            base[(size_t)m] = (int32_t)words.size();
+            for (int kk = 0; kk <= k + 1; ++kk) {
+                std::vector<uint64_t> w;
+                if (!gw_staircase_masks(m, kk, w)) abortm[(size_t)m] |= 1u << kk;
+                for (uint64_t x : w) words.push_back((u64)x);
+            }
+        }
+        env.sf.words = words.data(); env.sf.base_by_m = base.data(); env.sf.abort_by_m = abortm.data();
+        GwBatchView bv;
+        bv.bases = bases; bv.offsets = (const u64*)offsets; bv.k_by_m = k_by_m;
+
+        std::vector<std::vector<u64>> slab_store(n_reads);
+        std::vector<u64*> slabs(n_reads, nullptr);
+        std::vector<uint32_t> act[2], loc(2 * (size_t)n_reads + 2), ver(2 * (size_t)n_reads + 2);
+        act[0].resize(n_reads + 1); act[1].resize(n_reads + 1);
+        uint32_t ctr[4];
+        uint32_t max_m = 1;
+        for (uint32_t i = 0; i < n_reads; ++i) max_m = std::max<uint32_t>(max_m, (uint32_t)std::min<uint64_t>(offsets[i + 1] - offsets[i], GW_MAX_READ_LEN));
+        std::vector<GwU64x2> hist((size_t)(max_m + 2 * kmax + 2) * ((max_m + 63) / 64));
+
+        auto rounds = [&](std::vector<uint32_t> cur) {
+            int flip = 0;
+            while (!cur.empty()) {
+                memset(ctr, 0, sizeof(ctr));
+                GwRoundQueues rq;
+                rq.next_active = act[flip].data(); rq.locate_req = loc.data(); rq.verify_req = ver.data(); rq.counters = ctr;
+                for (uint32_t slot : cur) { GwSlab s(slabs[slot]); gw_run_read(env, s, slot, rq); }
+                for (uint32_t i = 0; i < ctr[1]; ++i) gw_locate_req(env.ix, slabs[loc[i] >> 1], loc[i] & 1u);
+                for (uint32_t i = 0; i < ctr[2]; ++i) gw_verify_req(env.ix, slabs[ver[i] >> 1], ver[i] & 1u, env.cfg.band_width, hist.data(), 1);
+                cur.assign(act[flip].begin(), act[flip].begin() + ctr[0]);
+                flip ^= 1;
+            }
+        };
+        auto pass = [&](const std::vector<uint32_t>& slots, uint32_t words_per_slab) {
+            const GwSlabParams sp = slab_params(words_per_slab);
+            for (uint32_t slot : slots) {
+                slab_store[slot].assign(words_per_slab, 0xDEADBEEFDEADBEEFULL);   // poison: the slab is not zero-initialised on the device
+                slabs[slot] = slab_store[slot].data();
+                gw_prep_read(bv, slabs[slot], sp, slot);
+                gw_scan_task(env.ix, reinterpret_cast<GwReadCtx*>(slabs[slot]), 0);
+                gw_scan_task(env.ix, reinterpret_cast<GwReadCtx*>(slabs[slot]), 1);
+            }
+            rounds(slots);
+        };
+        std::vector<uint32_t> all(n_reads);
+        for (uint32_t i = 0; i < n_reads; ++i) all[i] = i;
+        pass(all, slab_words);
+        *tiers_used = 0;
+        for (int tier = 1; tier < 3; ++tier) {
+            std::vector<uint32_t> over;
+            for (uint32_t i = 0; i < n_reads; ++i) if (reinterpret_cast<GwReadCtx*>(slabs[i])->status == GW_ST_OVERFLOW) over.push_back(i);
+            if (over.empty()) break;
+            *tiers_used += (uint32_t)over.size();
+            pass(over, tier == 1 ? slab_words * 8 : 262144);
+        }
+        // emit + SAM
+        std::string text;
+        for (uint32_t i = 0; i < n_reads; ++i) {
+            uint32_t nrec = 0, ncig = 0;
+            gw_emit_count(slabs[i], env.cfg, &nrec, &ncig);
+            std::vector<GwHitRec> recs(nrec);
+            std::vector<uint32_t> cigs(ncig + 1);
+            gw_emit_write(slabs[i], env.cfg, i, recs.data(), 0, nrec, cigs.data(), 0, ncig);
+            const GwReadCtx* c = reinterpret_cast<GwReadCtx*>(slabs[i]);
+            status[i] = recs.empty() ? -1 : recs[0].status;
+            const bool ok = status[i] == GW_ST_OK || status[i] == GW_ST_UNMAPPED;
+            counters[i * 4 + 0] = ok ? c->n_fm : -1; counters[i * 4 + 1] = ok ? c->n_sw : -1;
+            counters[i * 4 + 2] = ok ? c->n_cut : -1; counters[i * 4 + 3] = ok ? c->n_filt : -1;
+            lines[i] = 0;
+            if (!ok) continue;
+            const std::string name(names + name_off[i], (size_t)(name_off[i + 1] - name_off[i]));
+            size_t hidx = 0;
+            while (hidx < recs.size()) {
+                int n = 1;
+                while (hidx + (size_t)n < recs.size() && !recs[hidx + (size_t)n].is_head) ++n;
+                const size_t before = text.size();
+                gw_sam_one(S->host.contigs, name, bases + offsets[i], (size_t)(offsets[i + 1] - offsets[i]), quals ? quals + qual_off[i] : nullptr,
+                           quals ? (size_t)(qual_off[i + 1] - qual_off[i]) : 0, reinterpret_cast<const gw_hit_t*>(&recs[hidx]), std::min(n, 2), cigs.data(), text);
+                for (size_t p = before; p < text.size(); ++p) if (text[p] == '\n') lines[i]++;
+                hidx += (size_t)n;
+            }
+        }
+        char* o = (char*)malloc(text.size() + 1);
+        memcpy(o, text.c_str(), text.size() + 1);
+        return o;
+    } catch (std::exception& e) { g_err = e.what(); return nullptr; }
+}
+void gwsim_free(void* p) { free(p); }
+
+// alignBlockDetailed on an explicit pair through the device verifier body
+int gwsim_verify_pair(const char* ref, const char* query, int band_k, int* pos, int* nm, uint32_t* cig, int* cig_n) {
+    const int Ncols = (int)strlen(ref), m = (int)strlen(query);
+    auto qsym = [&](int j) -> int { return gw_code_of((unsigned char)query[j]); };
+    auto refsym = [&](int j) -> int { return gw_code_of((unsigned char)ref[j]); };
+    u64 peq[4][GW_MAX_NB];
+    memset(peq, 0, sizeof(peq));
+    for (int j = 0; j < m; ++j) {
+        int c = qsym(j);
+        if (c == 4) { for (int a = 0; a < 4; ++a) peq[a][j >> 6] |= 1ULL << (j & 63); }
+        else peq[c][j >> 6] |= 1ULL << (j & 63);
+    }
+    std::vector<GwU64x2> hist((size_t)(Ncols + 2) * std::max(1, (m + 63) / 64));
+    GwVerifyOut out;
+    gw_verify(m, Ncols, band_k, peq, refsym, qsym, hist.data(), 1, cig, &out);
+    *pos = out.pos; *nm = out.diff; *cig_n = out.cig_n;
+    return out.valid;
+}
+
+}  // extern "C"
