@@ -27,10 +27,10 @@ typedef unsigned long long u64;
 
 #define GW_MAX_READ_LEN 256
 #define GW_MAX_NB 4          // ceil(GW_MAX_READ_LEN / 64)
-#define GW_MAX_K 15          // NFA rows <= 16
+#define GW_MAX_K 25          // NFA rows <= 26: covers the default -k 0.1 for every supported read length
 #define GW_MAX_ROWS (GW_MAX_K + 1)
 #define GW_SSA_L 32          // SparseSuffixArray sampling (BWTransform.java:141)
-#define GW_CIG_CAP 36        // cigar elements kept per verified fragment (>= 2*GW_MAX_K + 3)
+#define GW_CIG_CAP 56        // cigar elements kept per verified fragment (>= 2*GW_MAX_K + 3)
 #define GW_MAX_WINDOW (GW_MAX_READ_LEN + 2 * GW_MAX_K + 2)
 
 // special chr ids / status codes (mirrored in include/gw_align.h)

@@ -28,7 +28,7 @@ extern "C" {
 #define GW_READ_MAPPED 0
 #define GW_READ_UNMAPPED 1
 #define GW_READ_REF_ABORT 2   /* the reference implementation throws on this read */
-#define GW_READ_UNSUPPORTED 3 /* outside the supported domain (read length 0 or > 256, k > 15) */
+#define GW_READ_UNSUPPORTED 3 /* outside the supported domain (read length 0 or > 256, k > 25) */
 
 /* special chr_id values (ReadHit.chr): */
 #define GW_CHR_NULL (-1)  /* Java null  (soft-clipped fragment, BidirectionalSuffixFilter.java:505-508) */

@@ -1,0 +1,103 @@
+"""CPU-side check of the device automaton logic: the per-thread kernel bodies of the product, compiled for the host by the
+test-only simulator (tests/hostsim), against the oracle. The real parity tests (CUDA path through the C-ABI) are in
+test_gpu_parity.py; this file exists so that logic errors are caught on a machine without a GPU."""
+import os
+
+import pytest
+
+import hostsim_lib as H
+import oracle_lib as O
+from genome_weaver_align_b200 import synth
+
+
+def _mk(tmp, name, contigs):
+    fa = os.path.join(str(tmp), name)
+    synth.write_fasta(fa, contigs)
+    O.OracleIndex.build_files(fa)
+    return fa, O.OracleIndex.load(fa), H.SimIndex(fa)
+
+
+def _compare(oi, si, reads, slab_words=4096, **cfg):
+    names = ["r%d" % i for i in range(len(reads))]
+    quals = ["I" * len(r) for r in reads]
+    ro = oi.align(names, reads, quals, **cfg)
+    rs = si.align(names, reads, quals, slab_words=slab_words, **cfg)
+    bad = [i for i in range(len(reads)) if ro["sam"][i] != rs["sam"][i] or ro["status"][i] != rs["status"][i] or ro["counters"][i] != rs["counters"][i]]
+    assert not bad, (bad[:5], ro["sam"][bad[0]], rs["sam"][bad[0]], ro["counters"][bad[0]], rs["counters"][bad[0]])
+    return ro, rs
+
+
+@pytest.fixture(scope="module")
+def rnd(tmp_path_factory):
+    g = synth.random_genome(50_000, 2, n_frac=0.01)
+    fa, oi, si = _mk(tmp_path_factory.mktemp("rnd"), "g.fa", [("chr1", g[:30_000]), ("chr2", g[30_000:])])
+    yield g, oi, si
+    oi.close()
+    si.close()
+
+
+def test_rank_locate(rnd):
+    g, oi, si = rnd
+    for w in (0, 1):
+        for p in [0, 1, 127, 128, 129, 5000, 49_999, 50_000, 50_007]:
+            assert oi.rank_acgtn(w, p) == si.rank_acgtn(w, p)
+        for r in [0, 1, 31, 32, 33, 777, 49_999]:
+            assert oi.locate(w, r) == si.locate(w, r)
+
+
+@pytest.mark.parametrize("k,length,n", [(2, 100, 400), (3, 100, 400), (3, 36, 150), (3, 155, 120), (6, 150, 80), (0.1, 100, 100), (0, 50, 100)])
+def test_sam_parity(rnd, k, length, n):
+    g, oi, si = rnd
+    _compare(oi, si, synth.simulate_reads(g, n, length, int(k) if k >= 1 else 6, length + int(10 * k)), k=k)
+
+
+def test_abort_domain_and_small_slabs(rnd):
+    g, oi, si = rnd
+    ro, rs = _compare(oi, si, synth.simulate_reads(g, 60, 250, 6, 9), k=6)
+    assert 2 in ro["status"]
+    ro, rs = _compare(oi, si, synth.simulate_reads(g, 200, 100, 3, 12), slab_words=1024, k=3)
+    assert rs["overflow_reads"] > 0   # the larger work-area tiers were exercised
+
+
+def test_edge_reads(rnd):
+    g, oi, si = rnd
+    s = g.tobytes().decode()
+    reads = [s[1000:1100], s[5:41], "N" * 50, s[2000:2150], "ACGT", "A", s[0:100], s[-100:], s[29_950:30_050], s[3000:3050] + "NN" + s[3052:3100],
+             O.revcomp(s[7000:7250]), s[-60:] + s[:40], "ACGTNNNNACGT"]
+    _compare(oi, si, reads, k=3)
+    _compare(oi, si, reads, k=0.1)
+
+
+def test_repeats_and_low_complexity(tmp_path):
+    g2 = synth.inject_repeats(synth.random_genome(60_000, 4), 5, families=5, min_len=200, max_len=800, copies=(5, 20))
+    fa, oi, si = _mk(tmp_path, "rep.fa", [("c", g2)])
+    _compare(oi, si, synth.simulate_reads(g2, 300, 100, 3, 6), k=3, report_type=1)
+    _compare(oi, si, synth.simulate_reads(g2, 150, 100, 3, 7), k=3, report_type=2, top_l=3)
+    _compare(oi, si, synth.simulate_reads(g2, 150, 100, 3, 8), k=3, num_split_allowed=0)
+    g3 = synth.low_complexity_genome(40_000, 5)
+    fa, oi3, si3 = _mk(tmp_path, "lc.fa", [("lc", g3)])
+    for L in (36, 75, 125):
+        _compare(oi3, si3, synth.simulate_reads(g3, 120, L, 3, L), k=3, report_type=1)
+
+
+def test_verifier_body_against_oracle():
+    import random
+    rnd_ = random.Random(5)
+    for _ in range(300):
+        m = rnd_.randint(1, 250)
+        q = "".join(rnd_.choice("ACGT") for _ in range(m))
+        ref = list("".join(rnd_.choice("ACGT") for _ in range(rnd_.randint(0, 8))) + q + "".join(rnd_.choice("ACGT") for _ in range(rnd_.randint(0, 8))))
+        for _e in range(rnd_.randint(0, 6)):
+            p = rnd_.randrange(len(ref))
+            r = rnd_.random()
+            if r < 0.5:
+                ref[p] = rnd_.choice("ACGTN")
+            elif r < 0.75:
+                ref.insert(p, rnd_.choice("ACGT"))
+            else:
+                del ref[p]
+        ref = "".join(ref)
+        a, b = O.align_block_detailed(ref, q, 31), H.verify_pair(ref, q, 31)
+        assert (a is None) == (b is None)
+        if a:
+            assert (a["cigar"], a["pos"], a["nm"]) == (b["cigar"], b["pos"], b["nm"]), (ref, q)
