@@ -139,30 +139,38 @@ GW_HD const u64* gw_staircase_for(const GwSearchEnv& env, GwReadCtx* c, int* kk)
     return env.sf.words + env.sf.base_by_m[m] + nb * (mm * (mm + 1) / 2);
 }
 
-// Runs one read until it finishes or parks. max_steps bounds the FM searches per call (0 = unbounded).
-GW_HD void gw_run_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
+// ---- resumable driver ------------------------------------------------------------------------------------
+// A read is advanced by gw_resume_read (once, when a thread picks the read up: consumes locate/verify results, seeds the
+// queue) followed by gw_step_read calls, each of which is ONE iteration of the reference's `while (!queue.isEmpty())` loop
+// (:352-475). Splitting the loop body out lets the search kernel keep all lanes of a warp busy: a lane whose read parks or
+// finishes fetches the next read instead of idling until the slowest read of the warp is done.
+#define GW_STEP_CONTINUE 0
+#define GW_STEP_PARKED 1
+#define GW_STEP_DONE 2
+
+// returns GW_STEP_CONTINUE when the read is in the best-first loop and wants gw_step_read calls
+GW_HD int gw_resume_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
     GwReadCtx* c = s.ctx();
-    uint32_t* occ_lookups = &c->occ_search;
     const int m = c->m, k = c->k;
     const GwDevConfig& cfg = env.cfg;
-
+    if (c->phase == GW_PH_DONE) return GW_STEP_DONE;
     if (c->phase == GW_PH_WAIT_EXACT) {  // reportExactMatchAlignment after the locate
         const int strand = c->pend[0].state_off;
         long long pos = strand == 0 ? (long long)env.ix.N - (long long)c->pend[0].textpos : (long long)c->pend[0].textpos;
         if (strand == 0) pos -= m;
         pos += 1;
         int chr, p;
-        if (pos < 0 || !gw_translate(env.ix, pos, &chr, &p)) { gw_fail(c, GW_ST_ABORT); return; }
+        if (pos < 0 || !gw_translate(env.ix, pos, &chr, &p)) { gw_fail(c, GW_ST_ABORT); return GW_STEP_DONE; }
         uint32_t cg = ((uint32_t)m << 4) | GW_OP_M;
         int32_t h = gw_new_hit(s, chr, p, m, 0, m, 0, strand, &cg, 1, (int32_t)(c->scan_ub[strand] - c->scan_lb[strand]));
-        if (h < 0 || !gw_add_result(s, cfg, h)) { gw_fail(c, GW_ST_OVERFLOW); return; }
+        if (h < 0 || !gw_add_result(s, cfg, h)) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
         c->phase = GW_PH_DONE;
-        return;
+        return GW_STEP_DONE;
     }
     if (c->phase == GW_PH_WAIT_VERIFY) {
         c->phase = GW_PH_RUN;
         gw_finish_report(env, s);
-        if (c->phase == GW_PH_DONE) return;
+        if (c->phase == GW_PH_DONE) return GW_STEP_DONE;
     }
     if (c->phase == GW_PH_INIT) {
         for (int strand = 0; strand < 2; ++strand) {
@@ -176,112 +184,127 @@ GW_HD void gw_run_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, c
                 rq.locate_req[gw_atomic_add(&rq.counters[1], 1u)] = slot * 2u;
                 rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
                 c->phase = GW_PH_WAIT_EXACT;
-                return;
+                return GW_STEP_PARKED;
             }
         }
-        if (k == 0) { c->phase = GW_PH_DONE; return; }
+        if (k == 0) { c->phase = GW_PH_DONE; return GW_STEP_DONE; }
         gw_build_masks(s);
         for (int strand = 0; strand < 2; ++strand) {
             if (c->scan_mm[strand] <= k) {
                 int ls = c->scan_ls[strand];
                 int32_t st = (ls != 0 && ls < m) ? gw_initial_state(env, s, strand, GW_DIR_BF, 0, m, ls, ls, k, 0, c->scan_mm[strand])
                                                  : gw_initial_state(env, s, strand, GW_DIR_F, 0, m, 0, 0, k, 0, c->scan_mm[strand]);
-                if (st < 0 || !gw_queue_add(s, cfg, st)) { gw_fail(c, GW_ST_OVERFLOW); return; }
+                if (st < 0 || !gw_queue_add(s, cfg, st)) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
             }
         }
         c->phase = GW_PH_RUN;
     }
+    return GW_STEP_CONTINUE;
+}
 
-    const int fmIndexSearchUpperBound = m * 20;
-    while (c->qn > 0) {
-        if (c->n_fm > fmIndexSearchUpperBound) break;
-        const int32_t base = gw_queue_poll(s, cfg);
-        int32_t c_off = base;
-        {
-            int32_t next = c_off;
-            bool report = false;
-            for (;;) {
-                const GwState* ns = gw_st(s, next);
-                if (!(gw_has_hit(ns) || gw_is_clipped(ns) || gw_remaining(ns) == 0)) break;
-                if (ns->next_split < 0) { report = true; break; }
-                next = ns->next_split;
-            }
-            if (report) {
-                if (gw_begin_report(env, s, slot, base, rq)) {
-                    c->phase = GW_PH_WAIT_VERIFY;
-                    rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
-                    return;
-                }
-                gw_finish_report(env, s);
-                if (c->phase == GW_PH_DONE) return;
-                continue;
-            }
-            c_off = next;
+// parks a running read without a request: it is simply continued in the next round (used to bound the tail of a launch)
+GW_HD void gw_yield_read(const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
+    (void)s;
+    rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
+}
+
+// one iteration of the best-first loop
+GW_HD int gw_step_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
+    GwReadCtx* c = s.ctx();
+    const int m = c->m, k = c->k;
+    const GwDevConfig& cfg = env.cfg;
+    uint32_t* occ_lookups = &c->occ_search;
+    if (c->qn <= 0 || c->n_fm > m * 20) { c->phase = GW_PH_DONE; return GW_STEP_DONE; }   // queue empty / fmIndexSearchUpperBound
+    const int32_t base = gw_queue_poll(s, cfg);
+    int32_t c_off = base;
+    {
+        int32_t next = c_off;
+        bool report = false;
+        for (;;) {
+            const GwState* ns = gw_st(s, next);
+            if (!(gw_has_hit(ns) || gw_is_clipped(ns) || gw_remaining(ns) == 0)) break;
+            if (ns->next_split < 0) { report = true; break; }
+            next = ns->next_split;
         }
-        GwState* cs = gw_st(s, c_off);
-        if (gw_is_finished(cs)) continue;
-        const int nm = gw_lower_k(cs);
-        if (nm > c->min_mm) { c->n_cut++; continue; }
-        if (c->min_mm - nm < 0) continue;
-        {
-            int scoreUB = gw_score(s, cfg, gw_st(s, base), true);
-            if (scoreUB < 0 || scoreUB < c->best_score) { c->n_cut++; continue; }
-        }
-        const int strand = gw_strand(cs);
-        const int nextBase = gw_q_symbol(c, strand, gw_next_index(cs));
-        bool advanced = false;
-        if (!((cs->state >> nextBase) & 1)) {
-            cs->state |= 1 << nextBase;
-            if (!gw_si_is_empty(cs, nextBase)) {
-                GwSiSet nsi;
-                gw_next_si(env.ix, cs, nextBase, &nsi, occ_lookups);
-                c->n_fm++;
-                int kk;
-                const u64* tbl = gw_staircase_for(env, c, &kk);
-                if (!tbl) return;
-                int32_t ns = gw_next_state(env, s, c_off, nextBase, nsi, tbl, kk);
-                if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return; }
-                if (ns >= 0) {
-                    if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return; }
-                    advanced = true;
-                } else c->n_filt++;
+        if (report) {
+            if (gw_begin_report(env, s, slot, base, rq)) {
+                c->phase = GW_PH_WAIT_VERIFY;
+                rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
+                return GW_STEP_PARKED;
             }
+            gw_finish_report(env, s);
+            return c->phase == GW_PH_DONE ? GW_STEP_DONE : GW_STEP_CONTINUE;
         }
-        if (advanced) continue;
-        {
+        c_off = next;
+    }
+    GwState* cs = gw_st(s, c_off);
+    if (gw_is_finished(cs)) return GW_STEP_CONTINUE;
+    const int nm = gw_lower_k(cs);
+    if (nm > c->min_mm) { c->n_cut++; return GW_STEP_CONTINUE; }
+    if (c->min_mm - nm < 0) return GW_STEP_CONTINUE;
+    {
+        int scoreUB = gw_score(s, cfg, gw_st(s, base), true);
+        if (scoreUB < 0 || scoreUB < c->best_score) { c->n_cut++; return GW_STEP_CONTINUE; }
+    }
+    const int strand = gw_strand(cs);
+    const int nextBase = gw_q_symbol(c, strand, gw_next_index(cs));
+    if (!((cs->state >> nextBase) & 1)) {
+        cs->state |= 1 << nextBase;
+        if (!gw_si_is_empty(cs, nextBase)) {
+            GwSiSet nsi;
+            gw_next_si(env.ix, cs, nextBase, &nsi, occ_lookups);
+            c->n_fm++;
             int kk;
             const u64* tbl = gw_staircase_for(env, c, &kk);
-            if (!tbl) return;
-            for (int ch = 0; ch < 4; ++ch) {
-                cs = gw_st(s, c_off);
-                if ((cs->state >> ch) & 1) continue;
-                cs->state |= 1 << ch;
-                if (gw_si_is_empty(cs, ch)) continue;
-                GwSiSet nsi;
-                gw_next_si(env.ix, cs, ch, &nsi, occ_lookups);
-                c->n_fm++;
-                int32_t ns = gw_next_state(env, s, c_off, ch, nsi, tbl, kk);
-                if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return; }
-                if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return; } }
-                else c->n_filt++;
+            if (!tbl) return GW_STEP_DONE;
+            int32_t ns = gw_next_state(env, s, c_off, nextBase, nsi, tbl, kk);
+            if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+            if (ns >= 0) {
+                if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+                return GW_STEP_CONTINUE;
             }
-        }
-        cs = gw_st(s, c_off);
-        cs->state |= 1 << 4;
-        if (gw_num_split(s, gw_st(s, base)) < cfg.num_split_allowed && nm + 1 <= c->min_mm) {
-            const int index = gw_next_index(cs);
-            if (index > cfg.indel_end_skip && m - index >= cfg.indel_end_skip) {
-                int32_t ns = gw_split_state(env, s, c_off, k, false);
-                if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return; }
-                if (ns == -3) { gw_fail(c, GW_ST_ABORT); return; }
-                if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return; } }
-                else c->n_filt++;
-                int32_t cl = gw_split_state(env, s, c_off, k, true);
-                if (cl == -2) { gw_fail(c, GW_ST_OVERFLOW); return; }
-                if (cl == -3) { gw_fail(c, GW_ST_ABORT); return; }
-                if (cl >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, cl))) { gw_fail(c, GW_ST_OVERFLOW); return; } }
-            }
+            c->n_filt++;
         }
     }
-    c->phase = GW_PH_DONE;
+    {
+        int kk;
+        const u64* tbl = gw_staircase_for(env, c, &kk);
+        if (!tbl) return GW_STEP_DONE;
+        for (int ch = 0; ch < 4; ++ch) {
+            cs = gw_st(s, c_off);
+            if ((cs->state >> ch) & 1) continue;
+            cs->state |= 1 << ch;
+            if (gw_si_is_empty(cs, ch)) continue;
+            GwSiSet nsi;
+            gw_next_si(env.ix, cs, ch, &nsi, occ_lookups);
+            c->n_fm++;
+            int32_t ns = gw_next_state(env, s, c_off, ch, nsi, tbl, kk);
+            if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+            if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
+            else c->n_filt++;
+        }
+    }
+    cs = gw_st(s, c_off);
+    cs->state |= 1 << 4;
+    if (gw_num_split(s, gw_st(s, base)) < cfg.num_split_allowed && nm + 1 <= c->min_mm) {
+        const int index = gw_next_index(cs);
+        if (index > cfg.indel_end_skip && m - index >= cfg.indel_end_skip) {
+            int32_t ns = gw_split_state(env, s, c_off, k, false);
+            if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+            if (ns == -3) { gw_fail(c, GW_ST_ABORT); return GW_STEP_DONE; }
+            if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
+            else c->n_filt++;
+            int32_t cl = gw_split_state(env, s, c_off, k, true);
+            if (cl == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+            if (cl == -3) { gw_fail(c, GW_ST_ABORT); return GW_STEP_DONE; }
+            if (cl >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, cl))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
+        }
+    }
+    return GW_STEP_CONTINUE;
+}
+
+// Runs one read until it finishes or parks (sequential form of the two functions above).
+GW_HD void gw_run_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
+    int r = gw_resume_read(env, s, slot, rq);
+    while (r == GW_STEP_CONTINUE) r = gw_step_read(env, s, slot, rq);
 }

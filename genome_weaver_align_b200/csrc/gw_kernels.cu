@@ -14,6 +14,8 @@
 #include "gw_bodies.cuh"
 #include "gw_kernels.h"
 
+#define GW_SEARCH_THREADS 64
+
 // ---------------------------------------------------------------------------------------------------------
 __global__ void gw_prep_kernel(GwBatchView bv, u64* const* slabs, const uint32_t* slots, uint32_t n, uint32_t read_base, GwSlabParams sp) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -81,12 +83,46 @@ __global__ void __launch_bounds__(256) gw_scan_coop_kernel(GwIndexView ix, u64* 
     }
 }
 
-__global__ void gw_search_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active, GwRoundQueues rq) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_active) return;
-    uint32_t slot = active ? active[i] : i;
-    GwSlab s(slabs[slot]);
-    gw_run_read(env, s, slot, rq);
+// Persistent lanes with work refill: every lane owns one read at a time and performs one best-first iteration per trip of
+// the outer loop; a lane whose read parks (needs locate/verify) or finishes takes the next read of the round's work list
+// (warp-aggregated atomic). Once the list is drained a running read gets `tail_steps` more iterations, then yields to the
+// next round, so the end of a launch is not held up by the few reads with very long searches.
+__global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_search_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
+                                                                      GwRoundQueues rq, uint32_t* work_counter, uint32_t tail_steps) {
+    const unsigned full = 0xFFFFFFFFu;
+    const unsigned lane = threadIdx.x & 31u;
+    bool have = false, exhausted = false;
+    GwSlab s;
+    uint32_t slot = 0, budget = tail_steps;
+    for (;;) {
+        const unsigned need = __ballot_sync(full, !have && !exhausted);
+        if (need) {
+            uint32_t first = 0;
+            const int leader = __ffs(need) - 1;
+            if ((int)lane == leader) first = atomicAdd(work_counter, (uint32_t)__popc(need));
+            first = __shfl_sync(full, first, leader);
+            if (!have && !exhausted) {
+                const uint32_t idx = first + (uint32_t)__popc(need & ((1u << lane) - 1u));
+                if (idx < n_active) {
+                    slot = active ? active[idx] : idx;
+                    s = GwSlab(slabs[slot]);
+                    have = gw_resume_read(env, s, slot, rq) == GW_STEP_CONTINUE;
+                    budget = tail_steps;
+                } else
+                    exhausted = true;
+            }
+        }
+        const unsigned busy = __ballot_sync(full, have);
+        const bool drained = __any_sync(full, exhausted);
+        if (!busy) {
+            if (drained) break;
+            continue;
+        }
+        if (have) {
+            if (gw_step_read(env, s, slot, rq) != GW_STEP_CONTINUE) have = false;
+            else if (drained && --budget == 0) { gw_yield_read(s, slot, rq); have = false; exhausted = true; }
+        }
+    }
 }
 
 __global__ void gw_locate_kernel(GwIndexView ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
@@ -234,8 +270,12 @@ void gwk_scan(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const u
     if (coop) gw_scan_coop_kernel<<<gw_grid(n_tasks * 4, 256), 256, 0, st>>>(ix, slabs, slots, (uint32_t)n_tasks);
     else gw_scan_kernel<<<gw_grid(n_tasks, 128), 128, 0, st>>>(ix, slabs, slots, (uint32_t)n_tasks);
 }
-void gwk_search(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, const GwRoundQueues& rq) {
-    if (n_active) gw_search_kernel<<<gw_grid(n_active, 64), 64, 0, st>>>(env, slabs, active, n_active, rq);
+void gwk_search(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, const GwRoundQueues& rq,
+                uint32_t* work_counter, uint32_t tail_steps, uint32_t max_blocks) {
+    if (!n_active) return;
+    unsigned blocks = gw_grid(n_active, GW_SEARCH_THREADS);
+    if (blocks > max_blocks) blocks = max_blocks;
+    gw_search_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, rq, work_counter, tail_steps);
 }
 void gwk_locate(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
     if (n) gw_locate_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, slabs, req, n);

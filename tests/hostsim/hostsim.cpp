@@ -105,6 +105,7 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
         std::vector<uint32_t> act[2], loc(2 * (size_t)n_reads + 2), ver(2 * (size_t)n_reads + 2);
         act[0].resize(n_reads + 1); act[1].resize(n_reads + 1);
         uint32_t ctr[4];
+        const uint32_t step_budget = getenv("GWSIM_STEP_BUDGET") ? (uint32_t)atoi(getenv("GWSIM_STEP_BUDGET")) : 0;
         uint32_t max_m = 1;
         for (uint32_t i = 0; i < n_reads; ++i) max_m = std::max<uint32_t>(max_m, (uint32_t)std::min<uint64_t>(offsets[i + 1] - offsets[i], GW_MAX_READ_LEN));
         std::vector<GwU64x2> hist((size_t)(max_m + 2 * kmax + 2) * ((max_m + 63) / 64));
@@ -115,7 +116,15 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
                 memset(ctr, 0, sizeof(ctr));
                 GwRoundQueues rq;
                 rq.next_active = act[flip].data(); rq.locate_req = loc.data(); rq.verify_req = ver.data(); rq.counters = ctr;
-                for (uint32_t slot : cur) { GwSlab s(slabs[slot]); gw_run_read(env, s, slot, rq); }
+                for (uint32_t slot : cur) {   // like the search kernel: resume, then steps; a step budget emulates the tail yield
+                    GwSlab s(slabs[slot]);
+                    int r = gw_resume_read(env, s, slot, rq);
+                    uint32_t budget = step_budget;
+                    while (r == GW_STEP_CONTINUE) {
+                        r = gw_step_read(env, s, slot, rq);
+                        if (r == GW_STEP_CONTINUE && step_budget && --budget == 0) { gw_yield_read(s, slot, rq); break; }
+                    }
+                }
                 for (uint32_t i = 0; i < ctr[1]; ++i) gw_locate_req(env.ix, slabs[loc[i] >> 1], loc[i] & 1u);
                 for (uint32_t i = 0; i < ctr[2]; ++i) gw_verify_req(env.ix, slabs[ver[i] >> 1], ver[i] & 1u, env.cfg.band_width, hist.data(), 1);
                 cur.assign(act[flip].begin(), act[flip].begin() + ctr[0]);

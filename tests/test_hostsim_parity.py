@@ -59,6 +59,13 @@ def test_abort_domain_and_small_slabs(rnd):
     assert rs["overflow_reads"] > 0   # the larger work-area tiers were exercised
 
 
+def test_yielding_rounds(rnd, monkeypatch):
+    # the search kernel lets a long-running read yield to the next round; results must not depend on where it yields
+    g, oi, si = rnd
+    monkeypatch.setenv("GWSIM_STEP_BUDGET", "7")
+    _compare(oi, si, synth.simulate_reads(g, 200, 100, 3, 13), k=3)
+
+
 def test_edge_reads(rnd):
     g, oi, si = rnd
     s = g.tobytes().decode()
