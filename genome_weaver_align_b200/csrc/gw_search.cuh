@@ -40,52 +40,59 @@ GW_HD int gw_score(const GwSlab& s, const GwDevConfig& cfg, const GwState* st, b
     }
     return total;
 }
-// StateQueue comparator
-GW_HD int gw_compare(const GwSlab& s, const GwDevConfig& cfg, int32_t a, int32_t b) {
-    const GwState* o1 = gw_st(s, a);
-    const GwState* o2 = gw_st(s, b);
-    int diff = gw_priority(o1) - gw_priority(o2);
-    if (diff == 0) diff = -(gw_score(s, cfg, o1, false) - gw_score(s, cfg, o2, false));
-    if (diff == 0) diff = -(gw_processed(o1) - gw_processed(o2));
-    return diff;
+// StateQueue comparator (:133-165): priority ascending, then score descending, then processed bases descending, packed into
+// one integer so that "compare(a, b) < 0" is "key(a) < key(b)". A state's key cannot change while it is queued: cursor and
+// lower bound of k are fixed at construction, the lower bound is only rewritten on a polled head (reportAlignment :582) and a
+// head's split chain is only relinked (SearchState.update) between its poll and its re-insertion. So the key is computed once,
+// at insertion, and the heap never has to touch the states again.
+GW_HD u64 gw_state_key(const GwSlab& s, const GwDevConfig& cfg, int32_t off) {
+    const GwState* o = gw_st(s, off);
+    const int score = gw_score(s, cfg, o, false);
+    return ((u64)(uint32_t)gw_priority(o) << 44) | ((u64)(uint32_t)(0x8000000 - score) << 16) | (u64)(uint32_t)(0xFFFF - gw_processed(o));
 }
 // java.util.PriorityQueue.offer (siftUp) ; returns false on capacity overflow
 GW_HD bool gw_queue_add(const GwSlab& s, const GwDevConfig& cfg, int32_t e) {
     if (e < 0) return true;  // StateQueue.add(null) is a no-op
     GwReadCtx* c = s.ctx();
     int32_t* q = s.queue();
+    u64* qk = s.queue_keys();
     int k = c->qn;
     if ((uint32_t)k >= s.sp.queue_cap) return false;
     c->qn = k + 1;
+    const u64 ke = gw_state_key(s, cfg, e);
     while (k > 0) {
-        int parent = (k - 1) >> 1;
-        int32_t pe = q[parent];
-        if (gw_compare(s, cfg, e, pe) >= 0) break;
-        q[k] = pe;
+        const int parent = (k - 1) >> 1;
+        const u64 kp = qk[parent];
+        if (ke >= kp) break;
+        q[k] = q[parent]; qk[k] = kp;
         k = parent;
     }
-    q[k] = e;
+    q[k] = e; qk[k] = ke;
     return true;
 }
 // java.util.PriorityQueue.poll (siftDown)
 GW_HD int32_t gw_queue_poll(const GwSlab& s, const GwDevConfig& cfg) {
+    (void)cfg;
     GwReadCtx* c = s.ctx();
     int32_t* q = s.queue();
-    int n = --c->qn;
-    int32_t result = q[0];
-    int32_t x = q[n];
+    u64* qk = s.queue_keys();
+    const int n = --c->qn;
+    const int32_t result = q[0];
+    const int32_t x = q[n];
+    const u64 kx = qk[n];
     if (n != 0) {
-        int k = 0, half = n >> 1;
+        int k = 0;
+        const int half = n >> 1;
         while (k < half) {
             int child = (k << 1) + 1;
-            int32_t ce = q[child];
-            int right = child + 1;
-            if (right < n && gw_compare(s, cfg, ce, q[right]) > 0) ce = q[child = right];
-            if (gw_compare(s, cfg, x, ce) <= 0) break;
-            q[k] = ce;
+            u64 kc = qk[child];
+            const int right = child + 1;
+            if (right < n) { const u64 kr = qk[right]; if (kc > kr) { kc = kr; child = right; } }
+            if (kx <= kc) break;
+            q[k] = q[child]; qk[k] = kc;
             k = child;
         }
-        q[k] = x;
+        q[k] = x; qk[k] = kx;
     }
     return result;
 }

@@ -51,9 +51,11 @@ struct GwSlab {
     GW_HD GwSlab(u64* b, const GwSlabParams& p) : base(b), sp(p) {}
     GW_HD GwReadCtx* ctx() const { return reinterpret_cast<GwReadCtx*>(base); }
     GW_HD u64* masks() const { return base + GW_CTX_WORDS; }
-    GW_HD int32_t* queue() const { return reinterpret_cast<int32_t*>(base + GW_CTX_WORDS + GW_MASK_WORDS); }
+    // priority queue: sort keys (comparator of StateQueue packed into one integer, cached at insertion) and state offsets
+    GW_HD u64* queue_keys() const { return base + GW_CTX_WORDS + GW_MASK_WORDS; }
+    GW_HD int32_t* queue() const { return reinterpret_cast<int32_t*>(base + GW_CTX_WORDS + GW_MASK_WORDS + sp.queue_cap); }
     GW_HD int32_t* hits() const { return queue() + sp.queue_cap; }
-    GW_HD uint32_t arena_begin() const { return GW_CTX_WORDS + GW_MASK_WORDS + (sp.queue_cap + sp.hit_cap + 1) / 2; }
+    GW_HD uint32_t arena_begin() const { return GW_CTX_WORDS + GW_MASK_WORDS + sp.queue_cap + (sp.queue_cap + sp.hit_cap + 1) / 2; }
     GW_HD u64* at(int32_t off) const { return base + off; }
 };
 
