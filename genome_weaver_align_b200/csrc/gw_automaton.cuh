@@ -14,33 +14,6 @@ struct GwRoundQueues {
 
 GW_HD void gw_fail(GwReadCtx* c, int status) { c->status = status; c->phase = GW_PH_DONE; }
 
-// build QueryMask pattern masks (F and reversed R) of q[0], q[1]  (QueryMask.java:41-63; reads hold no N here)
-GW_HD void gw_build_masks(const GwSlab& s) {
-    GwReadCtx* c = s.ctx();
-    const int m = c->m, nb = (m + 63) >> 6;
-    for (int strand = 0; strand < 2; ++strand) {
-        for (int ch = 0; ch < 4; ++ch) {
-            u64* f = gw_mask_ptr(s, strand, 0, ch);
-            u64* r = gw_mask_ptr(s, strand, 1, ch);
-            for (int b = 0; b < GW_MAX_NB; ++b) { f[b] = 0; r[b] = 0; }
-            for (int b = 0; b < nb; ++b) {
-                u64 lo = c->qlo[strand][b], hi = c->qhi[strand][b];
-                u64 valid = (b == nb - 1 && (m & 63)) ? ((1ULL << (m & 63)) - 1ULL) : ~0ULL;
-                f[b] = ((ch & 2) ? hi : ~hi) & ((ch & 1) ? lo : ~lo) & valid;
-            }
-            // R bit (m-1-i) = F bit i : reverse the nb*64-bit string, then shift right by nb*64 - m
-            u64 rev[GW_MAX_NB];
-            for (int b = 0; b < nb; ++b) rev[b] = gw_brev64(f[nb - 1 - b]);
-            const int sh = nb * 64 - m;  // 0..63
-            for (int b = 0; b < nb; ++b) {
-                u64 v = rev[b] >> sh;
-                if (sh && b + 1 < nb) v |= rev[b + 1] << (64 - sh);
-                r[b] = v;
-            }
-        }
-    }
-}
-
 GW_HD int gw_q_symbol(const GwReadCtx* c, int strand, int i) {
     return (int)((((c->qhi[strand][i >> 6] >> (i & 63)) & 1ULL) << 1) | ((c->qlo[strand][i >> 6] >> (i & 63)) & 1ULL));
 }
@@ -188,7 +161,6 @@ GW_HD int gw_resume_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot,
             }
         }
         if (k == 0) { c->phase = GW_PH_DONE; return GW_STEP_DONE; }
-        gw_build_masks(s);
         for (int strand = 0; strand < 2; ++strand) {
             if (c->scan_mm[strand] <= k) {
                 int ls = c->scan_ls[strand];
@@ -208,25 +180,20 @@ GW_HD void gw_yield_read(const GwSlab& s, uint32_t slot, const GwRoundQueues& rq
     rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
 }
 
-// one iteration of the best-first loop
+// one iteration of the best-first loop. The polled state is copied to registers once; all candidate extensions (the read's own
+// base first, then A,C,G,T) go through ONE FM step + NFA step + insertion site, which keeps the kernel small and lets the lanes
+// of a warp that are in the same loop trip run together.
 GW_HD int gw_step_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
     GwReadCtx* c = s.ctx();
     const int m = c->m, k = c->k;
     const GwDevConfig& cfg = env.cfg;
-    uint32_t* occ_lookups = &c->occ_search;
     if (c->qn <= 0 || c->n_fm > m * 20) { c->phase = GW_PH_DONE; return GW_STEP_DONE; }   // queue empty / fmIndexSearchUpperBound
     const int32_t base = gw_queue_poll(s, cfg);
     int32_t c_off = base;
-    {
-        int32_t next = c_off;
-        bool report = false;
-        for (;;) {
-            const GwState* ns = gw_st(s, next);
-            if (!(gw_has_hit(ns) || gw_is_clipped(ns) || gw_remaining(ns) == 0)) break;
-            if (ns->next_split < 0) { report = true; break; }
-            next = ns->next_split;
-        }
-        if (report) {
+    GwState C = gw_load_state(s, base);
+    for (;;) {   // first fragment of the chain that still has bases to process (:366-379)
+        if (!(gw_has_hit(&C) || gw_is_clipped(&C) || gw_remaining(&C) == 0)) break;
+        if (C.next_split < 0) {
             if (gw_begin_report(env, s, slot, base, rq)) {
                 c->phase = GW_PH_WAIT_VERIFY;
                 rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
@@ -235,69 +202,65 @@ GW_HD int gw_step_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, c
             gw_finish_report(env, s);
             return c->phase == GW_PH_DONE ? GW_STEP_DONE : GW_STEP_CONTINUE;
         }
-        c_off = next;
+        c_off = C.next_split;
+        C = gw_load_state(s, c_off);
     }
-    GwState* cs = gw_st(s, c_off);
-    if (gw_is_finished(cs)) return GW_STEP_CONTINUE;
-    const int nm = gw_lower_k(cs);
+    if (gw_is_finished(&C)) return GW_STEP_CONTINUE;
+    const int nm = gw_lower_k(&C);
     if (nm > c->min_mm) { c->n_cut++; return GW_STEP_CONTINUE; }
     if (c->min_mm - nm < 0) return GW_STEP_CONTINUE;
     {
-        int scoreUB = gw_score(s, cfg, gw_st(s, base), true);
+        const int scoreUB = gw_score(s, cfg, gw_st(s, base), true);
         if (scoreUB < 0 || scoreUB < c->best_score) { c->n_cut++; return GW_STEP_CONTINUE; }
     }
-    const int strand = gw_strand(cs);
-    const int nextBase = gw_q_symbol(c, strand, gw_next_index(cs));
-    if (!((cs->state >> nextBase) & 1)) {
-        cs->state |= 1 << nextBase;
-        if (!gw_si_is_empty(cs, nextBase)) {
-            GwSiSet nsi;
-            gw_next_si(env.ix, cs, nextBase, &nsi, occ_lookups);
-            c->n_fm++;
-            int kk;
-            const u64* tbl = gw_staircase_for(env, c, &kk);
-            if (!tbl) return GW_STEP_DONE;
-            int32_t ns = gw_next_state(env, s, c_off, nextBase, nsi, tbl, kk);
-            if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
-            if (ns >= 0) {
-                if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
-                return GW_STEP_CONTINUE;
-            }
-            c->n_filt++;
-        }
-    }
+    const int strand = gw_strand(&C);
+    const int nextBase = gw_q_symbol(c, strand, gw_next_index(&C));
+    // the staircase filter of the current minMismatches is needed on every path from here (:425, :439); where the reference's
+    // constructor throws, the read ends here whichever path asked for it
+    int kk;
+    const u64* tbl = gw_staircase_for(env, c, &kk);
+    if (!tbl) return GW_STEP_DONE;
+    u64 prev[GW_MAX_ROWS];
     {
-        int kk;
-        const u64* tbl = gw_staircase_for(env, c, &kk);
-        if (!tbl) return GW_STEP_DONE;
-        for (int ch = 0; ch < 4; ++ch) {
-            cs = gw_st(s, c_off);
-            if ((cs->state >> ch) & 1) continue;
-            cs->state |= 1 << ch;
-            if (gw_si_is_empty(cs, ch)) continue;
-            GwSiSet nsi;
-            gw_next_si(env.ix, cs, ch, &nsi, occ_lookups);
-            c->n_fm++;
-            int32_t ns = gw_next_state(env, s, c_off, ch, nsi, tbl, kk);
-            if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
-            if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
-            else c->n_filt++;
-        }
+        const u64* rows = gw_rows(gw_st(s, c_off));
+        for (int i = 0; i < C.height; ++i) prev[i] = rows[i];
     }
-    cs = gw_st(s, c_off);
-    cs->state |= 1 << 4;
+    int flags = C.state;
+    bool extended = false;   // the read's own base went through: the parent is dropped (:426-429)
+    int fail_status = 0;
+#pragma unroll 1
+    for (int t = 0; t < 5; ++t) {
+        const int ch = t == 0 ? nextBase : t - 1;
+        if ((flags >> ch) & 1) continue;
+        flags |= 1 << ch;
+        if (gw_si_is_empty(&C, ch)) continue;
+        GwSiSet nsi;
+        gw_next_si(env.ix, &C, ch, &nsi, &c->occ_search);
+        c->n_fm++;
+        const int32_t ns = gw_next_state(s, C, prev, ch, nsi, tbl, kk);
+        if (ns == -2) { fail_status = GW_ST_OVERFLOW; break; }
+        if (ns >= 0) {
+            if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { fail_status = GW_ST_OVERFLOW; break; }
+            if (t == 0) { extended = true; break; }
+        } else
+            c->n_filt++;
+    }
+    if (!extended) flags |= 1 << 4;
+    gw_st(s, c_off)->state = flags;   // checked-base flags live on the (possibly shared) state object
+    if (fail_status) { gw_fail(c, fail_status); return GW_STEP_DONE; }
+    if (extended) return GW_STEP_CONTINUE;
+    C.state = flags;
     if (gw_num_split(s, gw_st(s, base)) < cfg.num_split_allowed && nm + 1 <= c->min_mm) {
-        const int index = gw_next_index(cs);
+        const int index = gw_next_index(&C);
         if (index > cfg.indel_end_skip && m - index >= cfg.indel_end_skip) {
-            int32_t ns = gw_split_state(env, s, c_off, k, false);
-            if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
-            if (ns == -3) { gw_fail(c, GW_ST_ABORT); return GW_STEP_DONE; }
-            if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
-            else c->n_filt++;
-            int32_t cl = gw_split_state(env, s, c_off, k, true);
-            if (cl == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
-            if (cl == -3) { gw_fail(c, GW_ST_ABORT); return GW_STEP_DONE; }
-            if (cl >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, cl))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
+#pragma unroll 1
+            for (int clip = 0; clip < 2; ++clip) {   // nextStateAfterSplit, then nextStateAfterClipping (:462-472)
+                const int32_t ns = gw_split_state(env, s, C, k, clip != 0);
+                if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+                if (ns == -3) { gw_fail(c, GW_ST_ABORT); return GW_STEP_DONE; }
+                if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
+                else if (clip == 0) c->n_filt++;
+            }
         }
     }
     return GW_STEP_CONTINUE;

@@ -101,9 +101,12 @@ GW_HD int32_t gw_queue_poll(const GwSlab& s, const GwDevConfig& cfg) {
 GW_HD int32_t gw_alloc_state(const GwSlab& s, int height) {
     return gw_alloc(s, GW_STATE_WORDS + (uint32_t)height);
 }
+// whole-state copy from / to the arena (six 128-bit accesses; states are 16-byte aligned)
+GW_HD GwState gw_load_state(const GwSlab& s, int32_t off) { return *gw_st(s, off); }
 
 GW_HD void gw_set_init_siset(const GwIndexView& ix, GwState* st, int dir) {
     st->f_valid = st->b_valid = 0;
+    for (int i = 0; i < 4; ++i) { st->sif[i][0] = st->sif[i][1] = 0; st->sib[i][0] = st->sib[i][1] = 0; }
     if (dir == GW_DIR_F || dir == GW_DIR_BF) {
         st->f_valid = (uint8_t)ix.init_valid;
         for (int i = 0; i < 4; ++i) { st->sif[i][0] = ix.init_lb[i]; st->sif[i][1] = ix.init_ub[i]; }
@@ -117,18 +120,19 @@ GW_HD void gw_set_init_siset(const GwIndexView& ix, GwState* st, int dir) {
 
 // SearchState(k, null, cursor, priority): initial state with diagonal NFA (:753-757)
 GW_HD int32_t gw_initial_state(const GwSearchEnv& env, const GwSlab& s, int strand, int dir, int start, int end,
-                                                    int cursor, int pivot, int k, int minK, int priority) {
+                               int cursor, int pivot, int k, int minK, int priority) {
     int32_t off = gw_alloc_state(s, k + 1);
     if (off < 0) return -1;
-    GwState* st = gw_st(s, off);
-    st->start = (int16_t)start; st->end = (int16_t)end; st->cursor = (int16_t)cursor; st->pivot = (int16_t)pivot;
-    st->cflag = (uint8_t)(strand | (dir << 1));
-    gw_set_init_siset(env.ix, st, dir);
-    st->height = (uint8_t)(k + 1); st->k_offset = 0; st->has_cur = 0; st->has_nfa = 1;
-    st->state = gw_pack_state(4, minK, priority, false);
-    st->next_split = -1;
-    st->cur_lb = st->cur_ub = 0;
-    u64* rows = gw_rows(st);
+    GwState st;
+    st.start = (int16_t)start; st.end = (int16_t)end; st.cursor = (int16_t)cursor; st.pivot = (int16_t)pivot;
+    st.cflag = (uint8_t)(strand | (dir << 1));
+    gw_set_init_siset(env.ix, &st, dir);
+    st.height = (uint8_t)(k + 1); st.k_offset = 0; st.has_cur = 0; st.has_nfa = 1;
+    st.state = gw_pack_state(4, minK, priority, false);
+    st.next_split = -1;
+    st.cur_lb = st.cur_ub = 0;
+    *gw_st(s, off) = st;
+    u64* rows = gw_rows(gw_st(s, off));
     for (int i = 0; i <= k; ++i) rows[i] = jshl(1ULL, k + i);
     return off;
 }
@@ -151,6 +155,7 @@ GW_HD void gw_next_si(const GwIndexView& ix, const GwState* c, int ch, GwSiSet* 
     if (gw_dir(c) == GW_DIR_BF && c->cursor >= c->end - 1) hasF = false;
     const int strand = gw_strand(c);
     out->f_valid = out->b_valid = 0;
+    for (int i = 0; i < 4; ++i) { out->sif[i][0] = out->sif[i][1] = 0; out->sib[i][0] = out->sib[i][1] = 0; }
     if (!hasF && !hasB) { out->kind = GW_SI_EMPTY; return; }
     const int fm = hasF ? (strand == 0 ? 1 : 0) : (strand == 0 ? 0 : 1);
     const uint32_t lb = gw_clampN(ix, hasF ? c->sif[ch][0] : c->sib[ch][0]);
@@ -161,46 +166,41 @@ GW_HD void gw_next_si(const GwIndexView& ix, const GwState* c, int ch, GwSiSet* 
     if ((ub >> 7) == (lb >> 7)) gw_rank4(bl, ub & 127u, hi);  // same 64 B line: one load serves both queries
     else { GwBlk bu = gw_load_block(ix.occ[fm] + (ub >> 7)); gw_rank4(bu, ub & 127u, hi); }
     *occ_lookups += 2;
-    uint32_t (*dst)[2] = hasF ? out->sif : out->sib;
     uint8_t valid = 0;
+    uint32_t x = 0;
+    const uint32_t blb = c->sib[ch][0];
     for (int i = 0; i < 4; ++i) {
-        uint32_t l = ix.C[fm][i] + lo[i], u = ix.C[fm][i] + hi[i];
-        dst[i][0] = l; dst[i][1] = u;
+        const uint32_t l = ix.C[fm][i] + lo[i], u = ix.C[fm][i] + hi[i];
+        if (hasF) { out->sif[i][0] = l; out->sif[i][1] = u; } else { out->sib[i][0] = l; out->sib[i][1] = u; }
         if (l < u) valid |= (uint8_t)(1 << i);
-    }
-    if (hasF) {
-        out->f_valid = valid;
-        if (!hasB) { out->kind = GW_SI_F; return; }
-        uint32_t x = 0;
-        const uint32_t blb = c->sib[ch][0];
-        for (int i = 0; i < 4; ++i) {
-            uint32_t y = hi[i] - lo[i];
+        if (hasF && hasB) {
+            const uint32_t y = hi[i] - lo[i];
             out->sib[i][0] = blb + x; out->sib[i][1] = blb + x + y;
             x += y;
         }
-        out->b_valid = valid;
-        out->kind = GW_SI_BD;
+    }
+    if (hasF) {
+        out->f_valid = valid;
+        if (hasB) { out->b_valid = valid; out->kind = GW_SI_BD; } else out->kind = GW_SI_F;
     } else {
         out->b_valid = valid;
         out->kind = GW_SI_B;
     }
 }
 
-// ReadAlignmentNFA.nextState + SearchState.nextState: returns arena offset of the new state, -1 for "no match" (null),
-// -2 on slab overflow
-GW_HD int32_t gw_next_state(const GwSearchEnv& env, const GwSlab& s, int32_t c_off, int ch, const GwSiSet& nextSi,
-                                                 const u64* sf_tbl, int sf_kk) {
+// ReadAlignmentNFA.nextState + SearchState.nextState on a register copy `c` of the current state (rows in `prev`):
+// returns the arena offset of the new state, -1 for "no match" (null), -2 on slab overflow
+GW_HD int32_t gw_next_state(const GwSlab& s, const GwState& c, const u64* prev, int ch, const GwSiSet& nextSi,
+                            const u64* sf_tbl, int sf_kk) {
     GwReadCtx* ctx = s.ctx();
-    GwState* c = gw_st(s, c_off);
     const int m_read = ctx->m;
-    const int height = c->height;
-    const int kOffset = c->k_offset;
+    const int height = c.height;
+    const int kOffset = c.k_offset;
     const int k = kOffset + height - 1;
     const int kr = k - kOffset;
-    const u64 qeq = gw_pattern_mask64(s, gw_strand(c), m_read, gw_is_fwd(c), gw_next_index(c), c->pivot, c->cursor, ch, kr);
-    const int progressIndex = gw_processed(c);
-    const int fragmentLength = gw_frag_len(c);
-    const u64* prev = gw_rows(c);
+    const u64 qeq = gw_pattern_mask64(ctx, gw_strand(&c), m_read, gw_is_fwd(&c), gw_next_index(&c), c.pivot, c.cursor, ch, kr);
+    const int progressIndex = gw_processed(&c);
+    const int fragmentLength = gw_frag_len(&c);
     u64 next[GW_MAX_ROWS];
     int minKwithMatch = k + 1, minKwithProgress = k + 1;
     next[0] = (prev[0] & qeq) << 1;
@@ -230,84 +230,82 @@ GW_HD int32_t gw_next_state(const GwSearchEnv& env, const GwSlab& s, int32_t c_o
     const int newHeight = height - remove;
     int32_t off = gw_alloc_state(s, newHeight);
     if (off < 0) return -2;
-    c = gw_st(s, c_off);
-    GwState* n = gw_st(s, off);
+    GwState n;
     // Cursor.next
-    int nextCursor = c->cursor, d = gw_dir(c);
+    int nextCursor = c.cursor, d = gw_dir(&c);
     if (d == GW_DIR_F) ++nextCursor;
     else if (d == GW_DIR_B) --nextCursor;
-    else if (nextCursor + 1 < c->end) ++nextCursor;
-    else { d = GW_DIR_B; nextCursor = c->pivot; }
-    n->start = c->start; n->end = c->end; n->cursor = (int16_t)nextCursor; n->pivot = c->pivot;
-    n->cflag = (uint8_t)(gw_strand(c) | (d << 1));
+    else if (nextCursor + 1 < c.end) ++nextCursor;
+    else { d = GW_DIR_B; nextCursor = c.pivot; }
+    n.start = c.start; n.end = c.end; n.cursor = (int16_t)nextCursor; n.pivot = c.pivot;
+    n.cflag = (uint8_t)(gw_strand(&c) | (d << 1));
     // currentSi = nextCursor.isForwardSearch ? siTable.getForward(ch) : siTable.getBackward(ch)
-    bool fwd = d != GW_DIR_B;
-    bool has = fwd ? ((c->si_kind == GW_SI_F || c->si_kind == GW_SI_BD) && ((c->f_valid >> ch) & 1))
-                   : ((c->si_kind == GW_SI_B || c->si_kind == GW_SI_BD) && ((c->b_valid >> ch) & 1));
-    n->has_cur = has ? 1 : 0;
-    n->cur_lb = has ? (fwd ? c->sif[ch][0] : c->sib[ch][0]) : 0;
-    n->cur_ub = has ? (fwd ? c->sif[ch][1] : c->sib[ch][1]) : 0;
-    n->si_kind = nextSi.kind; n->f_valid = nextSi.f_valid; n->b_valid = nextSi.b_valid;
+    const bool fwd = d != GW_DIR_B;
+    const bool has = fwd ? ((c.si_kind == GW_SI_F || c.si_kind == GW_SI_BD) && ((c.f_valid >> ch) & 1))
+                         : ((c.si_kind == GW_SI_B || c.si_kind == GW_SI_BD) && ((c.b_valid >> ch) & 1));
+    n.has_cur = has ? 1 : 0;
+    n.cur_lb = has ? (fwd ? c.sif[ch][0] : c.sib[ch][0]) : 0;
+    n.cur_ub = has ? (fwd ? c.sif[ch][1] : c.sib[ch][1]) : 0;
+    n.si_kind = nextSi.kind; n.f_valid = nextSi.f_valid; n.b_valid = nextSi.b_valid;
     for (int i = 0; i < 4; ++i) {
-        n->sif[i][0] = nextSi.sif[i][0]; n->sif[i][1] = nextSi.sif[i][1];
-        n->sib[i][0] = nextSi.sib[i][0]; n->sib[i][1] = nextSi.sib[i][1];
+        n.sif[i][0] = nextSi.sif[i][0]; n.sif[i][1] = nextSi.sif[i][1];
+        n.sib[i][0] = nextSi.sib[i][0]; n.sib[i][1] = nextSi.sib[i][1];
     }
-    n->height = (uint8_t)newHeight; n->k_offset = (uint8_t)(kOffset + remove); n->has_nfa = 1;
-    n->state = gw_pack_state(ch, kOffset + remove, gw_priority(c), hasMatch);
-    n->next_split = c->next_split;
-    u64* nr = gw_rows(n);
+    n.height = (uint8_t)newHeight; n.k_offset = (uint8_t)(kOffset + remove); n.has_nfa = 1;
+    n.state = gw_pack_state(ch, kOffset + remove, gw_priority(&c), hasMatch);
+    n.next_split = c.next_split;
+    *gw_st(s, off) = n;
+    u64* nr = gw_rows(gw_st(s, off));
     if (remove == 0) { for (int h = 0; h < newHeight; ++h) nr[h] = prev[h]; }  // sic: the OLD automaton (ReadAlignmentNFA.java:206-207)
     else { for (int h = 0; h < newHeight; ++h) nr[h] = next[h + remove] >> 1; }
     return off;
 }
 
-// SearchState.nextStateAfterSplit (clip == false) / nextStateAfterClipping (clip == true); -1 null, -2 overflow, -3 abort
-GW_HD int32_t gw_split_state(const GwSearchEnv& env, const GwSlab& s, int32_t c_off, int k, bool clip) {
-    GwState* c = gw_st(s, c_off);
-    c->state |= 1 << 4;
-    const int minK = gw_lower_k(c);
+// SearchState.nextStateAfterSplit (clip == false) / nextStateAfterClipping (clip == true) on a register copy of the current
+// state; -1 null, -2 overflow, -3 abort
+GW_HD int32_t gw_split_state(const GwSearchEnv& env, const GwSlab& s, const GwState& c, int k, bool clip) {
+    const int minK = gw_lower_k(&c);
     if (!(minK < k)) return -1;
-    const int newHeight = (int)c->height - 1;
-    if (!c->has_nfa || newHeight < 0) return -3;
+    const int newHeight = (int)c.height - 1;
+    if (!c.has_nfa || newHeight < 0) return -3;
     // Cursor.split
-    const int d = gw_dir(c), strand = gw_strand(c);
+    const int d = gw_dir(&c), strand = gw_strand(&c);
     int ls, le, lc, lp, ld, rs, re, rc, rp, rd;
-    if (d == GW_DIR_F) { ls = c->start; le = c->cursor; lc = c->cursor; lp = c->pivot; ld = d; rs = c->cursor; re = c->end; rc = c->cursor; rp = c->cursor; rd = GW_DIR_F; }
-    else if (d == GW_DIR_B) { ls = c->cursor; le = c->end; lc = c->cursor; lp = c->pivot; ld = d; rs = c->start; re = c->cursor; rc = c->cursor; rp = c->start; rd = GW_DIR_B; }
+    if (d == GW_DIR_F) { ls = c.start; le = c.cursor; lc = c.cursor; lp = c.pivot; ld = d; rs = c.cursor; re = c.end; rc = c.cursor; rp = c.cursor; rd = GW_DIR_F; }
+    else if (d == GW_DIR_B) { ls = c.cursor; le = c.end; lc = c.cursor; lp = c.pivot; ld = d; rs = c.start; re = c.cursor; rc = c.cursor; rp = c.start; rd = GW_DIR_B; }
     else {
-        ls = c->start; le = c->cursor; lc = c->cursor; lp = c->pivot; ld = (c->cursor + 1 < c->end) ? d : GW_DIR_B;
-        rs = c->cursor; re = c->end; rc = c->cursor; rp = c->cursor; rd = d;
+        ls = c.start; le = c.cursor; lc = c.cursor; lp = c.pivot; ld = (c.cursor + 1 < c.end) ? d : GW_DIR_B;
+        rs = c.cursor; re = c.end; rc = c.cursor; rp = c.cursor; rd = d;
     }
     int32_t loff = gw_alloc_state(s, newHeight);
     if (loff < 0) return -2;
-    c = gw_st(s, c_off);
-    GwState* l = gw_st(s, loff);
-    l->start = (int16_t)ls; l->end = (int16_t)le; l->cursor = (int16_t)lc; l->pivot = (int16_t)lp;
-    l->cflag = (uint8_t)(strand | (ld << 1));
-    l->si_kind = c->si_kind; l->f_valid = c->f_valid; l->b_valid = c->b_valid;
-    for (int i = 0; i < 4; ++i) { l->sif[i][0] = c->sif[i][0]; l->sif[i][1] = c->sif[i][1]; l->sib[i][0] = c->sib[i][0]; l->sib[i][1] = c->sib[i][1]; }
-    l->has_cur = c->has_cur; l->cur_lb = c->cur_lb; l->cur_ub = c->cur_ub;
-    l->height = (uint8_t)newHeight; l->k_offset = (uint8_t)(c->k_offset + 1); l->has_nfa = 1;
-    l->state = gw_pack_state(gw_current_acgt(c), minK, gw_priority(c), gw_has_hit(c));
-    u64* lr = gw_rows(l);
-    for (int i = 0; i < newHeight; ++i) lr[i] = jshl(1ULL, newHeight + i - 1);  // ReadAlignmentNFA.nextStateAfterSplit
+    GwState l = c;   // currentSi, siTable are shared with the parent
+    l.start = (int16_t)ls; l.end = (int16_t)le; l.cursor = (int16_t)lc; l.pivot = (int16_t)lp;
+    l.cflag = (uint8_t)(strand | (ld << 1));
+    l.height = (uint8_t)newHeight; l.k_offset = (uint8_t)(c.k_offset + 1); l.has_nfa = 1;
+    l.state = gw_pack_state(gw_current_acgt(&c), minK, gw_priority(&c), gw_has_hit(&c));
     int32_t roff;
     if (!clip) {
-        roff = gw_initial_state(env, s, strand, rd, rs, re, rc, rp, k, minK, gw_priority(gw_st(s, c_off)));
+        roff = gw_initial_state(env, s, strand, rd, rs, re, rc, rp, k, minK, gw_priority(&c));
         if (roff < 0) return -2;
     } else {
         roff = gw_alloc_state(s, 0);
         if (roff < 0) return -2;
-        GwState* r = gw_st(s, roff);
-        r->start = (int16_t)rs; r->end = (int16_t)re; r->cursor = (int16_t)rc; r->pivot = (int16_t)rp;
-        r->cflag = (uint8_t)(strand | (rd << 1));
-        r->si_kind = GW_SI_NULL; r->f_valid = r->b_valid = 0;
-        r->has_cur = 0; r->cur_lb = r->cur_ub = 0;
-        r->height = 0; r->k_offset = 0; r->has_nfa = 0;
-        r->state = gw_pack_state(4, minK, gw_priority(gw_st(s, c_off)), false) | (1 << 25);
-        r->next_split = -1;
+        GwState r;
+        r.start = (int16_t)rs; r.end = (int16_t)re; r.cursor = (int16_t)rc; r.pivot = (int16_t)rp;
+        r.cflag = (uint8_t)(strand | (rd << 1));
+        r.si_kind = GW_SI_NULL; r.f_valid = r.b_valid = 0;
+        for (int i = 0; i < 4; ++i) { r.sif[i][0] = r.sif[i][1] = 0; r.sib[i][0] = r.sib[i][1] = 0; }
+        r.has_cur = 0; r.cur_lb = r.cur_ub = 0;
+        r.height = 0; r.k_offset = 0; r.has_nfa = 0;
+        r.state = gw_pack_state(4, minK, gw_priority(&c), false) | (1 << 25);
+        r.next_split = -1;
+        *gw_st(s, roff) = r;
     }
-    gw_st(s, loff)->next_split = roff;
+    l.next_split = roff;
+    *gw_st(s, loff) = l;
+    u64* lr = gw_rows(gw_st(s, loff));
+    for (int i = 0; i < newHeight; ++i) lr[i] = jshl(1ULL, newHeight + i - 1);  // ReadAlignmentNFA.nextStateAfterSplit
     return loff;
 }
 

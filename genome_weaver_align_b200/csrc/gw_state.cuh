@@ -41,7 +41,7 @@ struct GwReadCtx {
 };
 
 #define GW_CTX_WORDS ((uint32_t)((sizeof(GwReadCtx) + 7) / 8))
-#define GW_MASK_WORDS (2u * 2u * 4u * GW_MAX_NB)  // [strand][F/R][base][block]
+#define GW_MASK_WORDS 0u
 
 struct GwSlab {
     u64* base;
@@ -55,13 +55,10 @@ struct GwSlab {
     GW_HD u64* queue_keys() const { return base + GW_CTX_WORDS + GW_MASK_WORDS; }
     GW_HD int32_t* queue() const { return reinterpret_cast<int32_t*>(base + GW_CTX_WORDS + GW_MASK_WORDS + sp.queue_cap); }
     GW_HD int32_t* hits() const { return queue() + sp.queue_cap; }
-    GW_HD uint32_t arena_begin() const { return GW_CTX_WORDS + GW_MASK_WORDS + sp.queue_cap + (sp.queue_cap + sp.hit_cap + 1) / 2; }
+    GW_HD uint32_t arena_begin() const { return (GW_CTX_WORDS + GW_MASK_WORDS + sp.queue_cap + (sp.queue_cap + sp.hit_cap + 1) / 2 + 1u) & ~1u; }
     GW_HD u64* at(int32_t off) const { return base + off; }
 };
 
-GW_HD u64* gw_mask_ptr(const GwSlab& s, int strand, int rev, int ch) {
-    return s.masks() + (((strand * 2 + rev) * 4 + ch) * GW_MAX_NB);
-}
 
 // ---- search state node --------------------------------------------------------------------------------
 // si_kind: SiSet subclass
@@ -75,7 +72,7 @@ GW_HD u64* gw_mask_ptr(const GwSlab& s, int strand, int rev, int ch) {
 #define GW_DIR_B 1
 #define GW_DIR_BF 2
 
-struct GwState {
+struct alignas(16) GwState {
     int16_t start, end, cursor, pivot;   // Cursor
     uint8_t cflag;                       // strand | dir << 1
     uint8_t si_kind;
@@ -131,6 +128,7 @@ GW_HD uint32_t* gw_hit_cigar(GwHitNode* h) { return reinterpret_cast<uint32_t*>(
 // bump allocation; returns -1 (and flags the read for the large-slab pass) on overflow
 GW_HD int32_t gw_alloc(const GwSlab& s, uint32_t words) {
     GwReadCtx* c = s.ctx();
+    words = (words + 1u) & ~1u;   // nodes stay 16-byte aligned (128-bit loads/stores of whole states)
     uint32_t top = (uint32_t)c->top;
     if (top + words > s.sp.slab_words) return -1;
     c->top = (int32_t)(top + words);
@@ -149,24 +147,46 @@ GW_HD u64 gw_substring64(const u64* block, int nb, int start, int end) {
     return (high | low) & mask;
 }
 
-// QueryMask.getBidirectionalPatternMask64
-GW_HD u64 gw_pattern_mask64(const GwSlab& s, int strand, int m, bool dirIsForward, int nextIdx, int pivot,
-                                                 int cursor, int ch, int margin) {
+// QueryMask pattern vectors are not materialised: bit i of patternMaskF[ch] is (q[i] == ch), which is read straight from the
+// 2-bit planes of the read, and patternMaskR is patternMaskF mirrored (bit m-1-i), i.e. a bit reversal of a forward window.
+// 64 bits of patternMaskF[ch] starting at bit `start` (bits outside [0, m) are zero)
+GW_HD u64 gw_match_window(const u64* qlo, const u64* qhi, int m, int ch, int start) {
     const int nb = (m + 63) >> 6;
-    u64 p;
-    if (dirIsForward) {
-        const u64* f = gw_mask_ptr(s, strand, 0, ch);
-        int pos = nextIdx - margin;
-        if (pos < 0) p = jshl(gw_substring64(f, nb, 0, 64), -pos);
-        else p = gw_substring64(f, nb, pos, m);
-    } else {
-        const u64* r = gw_mask_ptr(s, strand, 1, ch);
-        int b = m - pivot;
-        int rshift = pivot - cursor - margin;
-        p = gw_substring64(r, nb, b, b + 64);
-        p = rshift >= 0 ? jushr(p, rshift) : jshl(p, -rshift);
+    int lsh = 0;
+    if (start < 0) {
+        if (start <= -64) return 0ULL;
+        lsh = -start; start = 0;
     }
-    return p;
+    const int w = start >> 6, off = start & 63;
+    if (w >= nb) return 0ULL;
+    u64 f0, f1 = 0ULL;
+    {
+        const u64 lo = qlo[w], hi = qhi[w];
+        const u64 valid = (w == nb - 1 && (m & 63)) ? ((1ULL << (m & 63)) - 1ULL) : ~0ULL;
+        f0 = ((ch & 2) ? hi : ~hi) & ((ch & 1) ? lo : ~lo) & valid;
+    }
+    if (off != 0 && w + 1 < nb) {
+        const u64 lo = qlo[w + 1], hi = qhi[w + 1];
+        const u64 valid = (w + 1 == nb - 1 && (m & 63)) ? ((1ULL << (m & 63)) - 1ULL) : ~0ULL;
+        f1 = ((ch & 2) ? hi : ~hi) & ((ch & 1) ? lo : ~lo) & valid;
+    }
+    u64 v = off ? ((f0 >> off) | (f1 << (64 - off))) : f0;
+    return v << lsh;
+}
+
+// QueryMask.getBidirectionalPatternMask64 (QueryMask.java:73-97) on the planes of q[strand]
+GW_HD u64 gw_pattern_mask64(const GwReadCtx* c, int strand, int m, bool dirIsForward, int nextIdx, int pivot, int cursor, int ch, int margin) {
+    const u64* qlo = c->qlo[strand];
+    const u64* qhi = c->qhi[strand];
+    if (dirIsForward) {
+        const int pos = nextIdx - margin;
+        if (pos < 0) return jshl(gw_match_window(qlo, qhi, m, ch, 0), -pos);   // substring64(0, 64) << -pos
+        return gw_match_window(qlo, qhi, m, ch, pos);                          // substring64(pos, m): bits >= m are already zero
+    }
+    // patternMaskR.substring64(m - pivot, m - pivot + 64): bit j = F[pivot - 1 - j]
+    u64 p = gw_brev64(gw_match_window(qlo, qhi, m, ch, pivot - 64));
+    const int rshift = pivot - cursor - margin;
+    return rshift >= 0 ? jushr(p, rshift) : jshl(p, -rshift);
 }
 
 // StaircaseFilter.getStairCaseMask64bit for the filter (m, kk); tbl points at the (kk+1) x nb words of that filter
