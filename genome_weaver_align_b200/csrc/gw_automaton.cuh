@@ -37,9 +37,11 @@ GW_HD bool gw_begin_report(const GwSearchEnv& env, const GwSlab& s, uint32_t slo
             pf->sa_index = st->cur_lb;
             // FMIndexOnGenome.toCoordinate: fm = ~(strand ^ (dir.isForward ? 0 : 1)) & 1
             pf->fm = ~(gw_strand(st) ^ (gw_is_fwd(st) ? 0 : 1)) & 1;
-            uint32_t id = slot * 2u + (uint32_t)n;
-            rq.locate_req[gw_atomic_add(&rq.counters[1], 1u)] = id;
-            rq.verify_req[gw_atomic_add(&rq.counters[2], 1u)] = id;
+            if (rq.counters) {   // round mode; the fused kernel serves the request on the same lane (gw_fused.cuh)
+                uint32_t id = slot * 2u + (uint32_t)n;
+                rq.locate_req[gw_atomic_add(&rq.counters[1], 1u)] = id;
+                rq.verify_req[gw_atomic_add(&rq.counters[2], 1u)] = id;
+            }
             need = true;
         }
     }
@@ -154,8 +156,10 @@ GW_HD int gw_resume_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot,
                 c->pend[0].sa_index = c->scan_lb[strand];
                 c->pend[0].fm = strand == 0 ? 1 : 0;  // FMIndexOnGenome.toCoordinate(saIndex, strand)
                 c->pend_n = 1;
-                rq.locate_req[gw_atomic_add(&rq.counters[1], 1u)] = slot * 2u;
-                rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
+                if (rq.counters) {
+                    rq.locate_req[gw_atomic_add(&rq.counters[1], 1u)] = slot * 2u;
+                    rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
+                }
                 c->phase = GW_PH_WAIT_EXACT;
                 return GW_STEP_PARKED;
             }
@@ -196,7 +200,7 @@ GW_HD int gw_step_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, c
         if (C.next_split < 0) {
             if (gw_begin_report(env, s, slot, base, rq)) {
                 c->phase = GW_PH_WAIT_VERIFY;
-                rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
+                if (rq.counters) rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
                 return GW_STEP_PARKED;
             }
             gw_finish_report(env, s);

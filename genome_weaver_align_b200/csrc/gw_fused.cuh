@@ -1,0 +1,181 @@
+// gw_fused.cuh — the whole per-read path as ONE resumable lane program: best-first search, SA locate and bit-vector DP
+// verification of a read are driven by the same lane, cut into short slices ("ticks") of one kind each. A warp runs, per
+// trip of its loop, the search slice for the lanes that are searching, the locate slice for those walking the suffix array,
+// the DP slice for those verifying, so every lane advances every trip and no read waits for a device-wide round.
+// Replaces the per-read sequence of AlignmentProcess.align_internal -> verify -> toCoordinate / alignBlockDetailed
+// (reference: align/src/main/java/org/utgenome/weaver/align/strategy/BidirectionalSuffixFilter.java:278-477, :496-560;
+// align/FMIndexOnGenome.java:227-252; align/SparseSuffixArray.java:141-161; align/BitParallelSmithWaterman.java:387-644).
+#pragma once
+#include "gw_bodies.cuh"
+
+#define GW_LP_FETCH 0    // lane has no read
+#define GW_LP_SEARCH 1   // one best-first iteration per tick
+#define GW_LP_LOCATE 2   // up to q_lf LF steps per tick
+#define GW_LP_DP 3       // up to q_cols DP columns per tick
+#define GW_LP_TRACE 4    // traceback + CIGAR of the finished DP
+
+struct GwFusedParams {
+    int32_t q_lf, q_cols;
+};
+
+GW_HD GwRoundQueues gw_no_queues() {
+    GwRoundQueues rq;
+    rq.next_active = nullptr; rq.locate_req = nullptr; rq.verify_req = nullptr; rq.counters = nullptr;
+    return rq;
+}
+
+// picks the next pending fragment that needs locate (+ verify), or resumes the automaton with the results
+GW_HD int gw_job_next(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, int from_frag) {
+    GwReadCtx* c = s.ctx();
+    for (;;) {
+        for (int f = from_frag; f < c->pend_n; ++f) {
+            if (c->pend[f].kind == 2) {
+                c->job.frag = f; c->job.lf_j = 0; c->job.lf_cursor = c->pend[f].sa_index;
+                return GW_LP_LOCATE;
+            }
+        }
+        const int r = gw_resume_read(env, s, slot, gw_no_queues());
+        if (r == GW_STEP_CONTINUE) return GW_LP_SEARCH;
+        if (r == GW_STEP_DONE) return GW_LP_FETCH;
+        from_frag = 0;   // parked again (exact hit waiting for its locate)
+    }
+}
+
+// a lane picked the read up: consumes the quick-scan results, seeds the queue (AlignmentProcess.align_internal :296-349)
+GW_HD int gw_fused_start(const GwSearchEnv& env, const GwSlab& s, uint32_t slot) {
+    const int r = gw_resume_read(env, s, slot, gw_no_queues());
+    if (r == GW_STEP_CONTINUE) return GW_LP_SEARCH;
+    if (r == GW_STEP_DONE) return GW_LP_FETCH;
+    return gw_job_next(env, s, slot, 0);
+}
+
+GW_HD int gw_fused_search_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t slot) {
+    const int r = gw_step_read(env, s, slot, gw_no_queues());
+    if (r == GW_STEP_CONTINUE) return GW_LP_SEARCH;
+    if (r == GW_STEP_DONE) return GW_LP_FETCH;
+    return gw_job_next(env, s, slot, 0);
+}
+
+// 64 window columns starting at text position p (bit j = position p + j; positions >= N read as 0)
+GW_HD u64 gw_plane_window(const u64* plane, uint32_t n_words, uint32_t p) {
+    const uint32_t w = p >> 6, off = p & 63u;
+    if (w >= n_words) return 0ULL;
+    u64 v = gw_ld64(plane + w) >> off;
+    if (off && w + 1 < n_words) v |= gw_ld64(plane + w + 1) << (64 - off);
+    return v;
+}
+
+// AlignmentProcess.verify, window + query set-up (:517-538); returns false when the fragment is finished without a DP
+GW_HD bool gw_job_begin_dp(const GwSearchEnv& env, const GwSlab& s, GwU64x2* hist, size_t stride) {
+    GwReadCtx* c = s.ctx();
+    GwJob* job = &c->job;
+    GwPendFrag* pf = &c->pend[job->frag];
+    const GwIndexView& ix = env.ix;
+    const GwState* st = gw_st(s, pf->state_off);
+    const int strand = gw_strand(st);
+    const int start = st->start, end = st->end;
+    const int fragLen = end - start;
+    const int k = c->k;
+    const long long seqIndex = pf->fm == 0 ? (long long)pf->textpos : (long long)ix.N - (long long)pf->textpos;
+    const long long x = seqIndex - gw_head_offset(st);
+    long long refStart = x - k; if (refStart < 0) refStart = 0;
+    long long refEnd = x + fragLen + k; if (refEnd > (long long)ix.N) refEnd = (long long)ix.N;
+    pf->ref_start = refStart;
+    pf->res_abort = 0;
+    if (refStart > refEnd) { pf->res_abort = 1; pf->res_valid = 0; return false; }  // ACGTSequence.subString throws
+    const int Ncols = (int)(refEnd - refStart);
+    // pattern masks of the fragment q[strand][start, end), reversed on the reverse strand (:529-534), from the read's bit planes
+    const int m = c->m;
+    const int nbf = gw_max(1, (fragLen + 63) >> 6);
+    for (int b = 0; b < GW_MAX_NB; ++b) {
+        const int rem = fragLen - 64 * b;
+        const u64 keep = rem >= 64 ? ~0ULL : (rem <= 0 ? 0ULL : ((1ULL << rem) - 1ULL));
+        for (int a = 0; a < 4; ++a) {
+            u64 v = 0ULL;
+            if (b < nbf && rem > 0) {
+                if (strand == 0) v = gw_match_window(c->qlo[0], c->qhi[0], m, a, start + 64 * b);
+                else v = gw_brev64(gw_match_window(c->qlo[1], c->qhi[1], m, a, end - 64 * (b + 1)));
+            }
+            job->peq[a][b] = v & keep;
+        }
+    }
+    const uint32_t n_words = (ix.N >> 6) + 1u;
+    for (int w = 0; w < GW_RW_WORDS; ++w) {
+        const int rem = Ncols - 64 * w;
+        if (rem <= 0) { job->rw_lo[w] = job->rw_hi[w] = job->rw_nf[w] = 0ULL; continue; }
+        const uint32_t p = (uint32_t)refStart + 64u * (uint32_t)w;
+        job->rw_lo[w] = gw_plane_window(ix.ref_lo, n_words, p);
+        job->rw_hi[w] = gw_plane_window(ix.ref_hi, n_words, p);
+        job->rw_nf[w] = gw_plane_window(ix.ref_nf, n_words, p);
+    }
+    GwDp d;
+    gw_dp_begin(d, fragLen, Ncols, env.cfg.band_width, hist, stride);
+    job->dp = d;
+    return true;
+}
+
+GW_HD int gw_job_ref_symbol(const GwJob* job, int j) {
+    const int w = j >> 6, sft = j & 63;
+    if ((job->rw_nf[w] >> sft) & 1ULL) return 4;
+    return (int)((((job->rw_hi[w] >> sft) & 1ULL) << 1) | ((job->rw_lo[w] >> sft) & 1ULL));
+}
+
+GW_HD int gw_fused_locate_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwFusedParams& fp, GwU64x2* hist, size_t stride) {
+    GwReadCtx* c = s.ctx();
+    GwJob* job = &c->job;
+    GwPendFrag* pf = &c->pend[job->frag];
+    const GwIndexView& ix = env.ix;
+    uint32_t cursor = job->lf_cursor;
+    int j = job->lf_j;
+    for (int q = 0; q < fp.q_lf && (cursor % GW_SSA_L) != 0; ++q) {
+        cursor = gw_suffix_link(ix, pf->fm, cursor);
+        ++j;
+    }
+    if ((cursor % GW_SSA_L) != 0) { job->lf_cursor = cursor; job->lf_j = j; return GW_LP_LOCATE; }
+    const uint32_t smp = gw_ld32(ix.ssa[pf->fm] + cursor / GW_SSA_L);
+    pf->textpos = j == 0 ? smp : (uint32_t)(((u64)smp + (u64)j + ix.N) % ix.N);
+    c->occ_locate += (uint32_t)j;
+    if (c->phase == GW_PH_WAIT_EXACT) return gw_job_next(env, s, slot, c->pend_n);   // exact hit: no verification (:490-494)
+    if (gw_job_begin_dp(env, s, hist, stride)) return GW_LP_DP;
+    return gw_job_next(env, s, slot, job->frag + 1);
+}
+
+GW_HD int gw_fused_dp_tick(const GwSearchEnv& env, const GwSlab& s, const GwFusedParams& fp, GwU64x2* hist, size_t stride) {
+    GwJob* job = &s.ctx()->job;
+    GwDp d = job->dp;
+    auto refsym = [&](int j) -> int { return gw_job_ref_symbol(job, j); };
+    gw_dp_columns(d, d.j + fp.q_cols, env.cfg.band_width, job->peq, refsym, hist, stride);
+    job->dp = d;
+    return d.j >= d.ncols ? GW_LP_TRACE : GW_LP_DP;
+}
+
+GW_HD int gw_fused_trace_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, GwU64x2* hist, size_t stride) {
+    GwReadCtx* c = s.ctx();
+    GwJob* job = &c->job;
+    GwPendFrag* pf = &c->pend[job->frag];
+    const GwState* st = gw_st(s, pf->state_off);
+    const int strand = gw_strand(st), start = st->start, end = st->end;
+    const u64* qlo = c->qlo[strand];
+    const u64* qhi = c->qhi[strand];
+    auto qsym = [&](int i) -> int {
+        const int p = strand == 0 ? start + i : end - 1 - i;
+        return (int)((((qhi[p >> 6] >> (p & 63)) & 1ULL) << 1) | ((qlo[p >> 6] >> (p & 63)) & 1ULL));
+    };
+    auto refsym = [&](int j) -> int { return gw_job_ref_symbol(job, j); };
+    GwVerifyOut out;
+    gw_dp_traceback(job->dp, refsym, qsym, hist, stride, pf->cig, &out);
+    pf->res_valid = out.valid; pf->res_pos = out.pos; pf->res_diff = out.diff; pf->res_cig_n = out.cig_n;
+    if (out.cig_overflow) pf->res_abort = 2;  // cannot happen within GW_MAX_K; reported as unsupported
+    return gw_job_next(env, s, slot, job->frag + 1);
+}
+
+// one tick of whatever the lane is doing; returns the lane's next state
+GW_HD int gw_fused_tick(int lp, const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwFusedParams& fp, GwU64x2* hist, size_t stride) {
+    switch (lp) {
+    case GW_LP_SEARCH: return gw_fused_search_tick(env, s, slot);
+    case GW_LP_LOCATE: return gw_fused_locate_tick(env, s, slot, fp, hist, stride);
+    case GW_LP_DP: return gw_fused_dp_tick(env, s, fp, hist, stride);
+    case GW_LP_TRACE: return gw_fused_trace_tick(env, s, slot, hist, stride);
+    default: return GW_LP_FETCH;
+    }
+}

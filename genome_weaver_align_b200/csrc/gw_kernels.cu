@@ -11,7 +11,7 @@
 // nothing here is a dense contraction).
 #include <cuda_runtime.h>
 
-#include "gw_bodies.cuh"
+#include "gw_fused.cuh"
 #include "gw_kernels.h"
 
 #define GW_SEARCH_THREADS 64
@@ -122,6 +122,47 @@ __global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_search_kernel(GwSearchEn
             if (gw_step_read(env, s, slot, rq) != GW_STEP_CONTINUE) have = false;
             else if (drained && --budget == 0) { gw_yield_read(s, slot, rq); have = false; exhausted = true; }
         }
+    }
+}
+
+// The whole per-read path on persistent lanes (gw_fused.cuh): a lane owns one read from its first search step to its last
+// verification. Per trip of the warp loop the lanes that search run one best-first iteration, those locating run a few LF
+// steps, those verifying a slice of DP columns; a lane whose read is finished takes the next one from the work list.
+__global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_fused_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
+                                                                     uint32_t* work_counter, GwU64x2* hist, GwFusedParams fp) {
+    const unsigned full = 0xFFFFFFFFu;
+    const unsigned lane = threadIdx.x & 31u;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int lp = GW_LP_FETCH;
+    bool exhausted = false;
+    GwSlab s;
+    uint32_t slot = 0;
+    for (;;) {
+        const unsigned need = __ballot_sync(full, lp == GW_LP_FETCH && !exhausted);
+        if (need) {
+            uint32_t first = 0;
+            const int leader = __ffs(need) - 1;
+            if ((int)lane == leader) first = atomicAdd(work_counter, (uint32_t)__popc(need));
+            first = __shfl_sync(full, first, leader);
+            if (lp == GW_LP_FETCH && !exhausted) {
+                const uint32_t idx = first + (uint32_t)__popc(need & ((1u << lane) - 1u));
+                if (idx < n_active) {
+                    slot = active ? active[idx] : idx;
+                    s = GwSlab(slabs[slot]);
+                    lp = gw_fused_start(env, s, slot);
+                } else
+                    exhausted = true;
+            }
+        }
+        if (!__any_sync(full, lp != GW_LP_FETCH)) {
+            if (__all_sync(full, exhausted)) break;
+            continue;
+        }
+        if (lp == GW_LP_SEARCH) lp = gw_fused_search_tick(env, s, slot);
+        else if (lp == GW_LP_LOCATE) lp = gw_fused_locate_tick(env, s, slot, fp, my_hist, stride);
+        else if (lp == GW_LP_DP) lp = gw_fused_dp_tick(env, s, fp, my_hist, stride);
+        else if (lp == GW_LP_TRACE) lp = gw_fused_trace_tick(env, s, slot, my_hist, stride);
     }
 }
 
@@ -276,6 +317,13 @@ void gwk_search(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, cons
     unsigned blocks = gw_grid(n_active, GW_SEARCH_THREADS);
     if (blocks > max_blocks) blocks = max_blocks;
     gw_search_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, rq, work_counter, tail_steps);
+}
+void gwk_fused(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
+               int q_lf, int q_cols, uint32_t blocks) {
+    if (!n_active) return;
+    GwFusedParams fp;
+    fp.q_lf = q_lf; fp.q_cols = q_cols;
+    gw_fused_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, fp);
 }
 void gwk_locate(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
     if (n) gw_locate_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, slabs, req, n);

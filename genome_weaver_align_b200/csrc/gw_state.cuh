@@ -9,6 +9,7 @@
 // split chains), so states live in a bump-allocated arena and are referred to by word offsets, never copied.
 #pragma once
 #include "gw_fm.cuh"
+#include "gw_verify.cuh"
 
 // ---- slab layout (8-byte words) -------------------------------------------------------------------------
 struct GwPendFrag {
@@ -24,6 +25,18 @@ struct GwPendFrag {
     uint32_t cig[GW_CIG_CAP];
 };
 
+// locate + verification of one pending fragment, resumable (fused kernel, gw_fused.cuh)
+#define GW_RW_WORDS ((GW_MAX_WINDOW + 63) / 64)
+struct GwJob {
+    int32_t frag;            // index into pend[]
+    int32_t lf_j;            // LF steps done so far
+    uint32_t lf_cursor;      // current SA row of the walk
+    int32_t pad_;
+    GwDp dp;
+    u64 peq[4][GW_MAX_NB];   // pattern masks of the query fragment
+    u64 rw_lo[GW_RW_WORDS], rw_hi[GW_RW_WORDS], rw_nf[GW_RW_WORDS];   // reference window planes, column 0 at bit 0
+};
+
 struct GwReadCtx {
     int32_t m, k;
     int32_t min_mm, max_match_len, best_score;
@@ -37,6 +50,7 @@ struct GwReadCtx {
     GwSlabParams sp;          // geometry of the slab this context lives in
     uint32_t occ_scan, occ_search, occ_locate;   // occurrence-table lookups done for this read (roofline work unit)
     GwPendFrag pend[2];
+    GwJob job;
     u64 qlo[2][GW_MAX_NB], qhi[2][GW_MAX_NB];  // q[0] = read, q[1] = its complement, N replaced by A in both
 };
 

@@ -15,29 +15,42 @@ struct GwVerifyOut {
 };
 
 
+// Resumable form: the DP over the window columns can be advanced in slices (gw_dp_columns) so that the fused alignment kernel
+// can interleave it with the search steps of other lanes; gw_verify runs the three stages back to back.
+struct GwDp {
+    int32_t m, ncols, bmax, j, bceil, has_best, best_tail, best_diff;
+    int32_t D[GW_MAX_NB];
+    u64 vp[GW_MAX_NB], vn[GW_MAX_NB];   // column j values of the active blocks
+};
+
+GW_HD int gw_score_boundary(int m, int band_k, int r) { return gw_max(m - ((r + 1) * 64) + band_k, 0); }
+
 // hist: scratch base for this request; element (col, blk) at hist[((col * bMax + blk) * stride)] as GwU64x2 (vp, vn)
-// peq: [4][bMax] pattern masks of the query (bits >= m clear); refsym(j): reference symbol (0..4) of window column j
-// qsym(i): query symbol (0..4) of row i
-template <typename RefSym, typename QSym>
-GW_HD void gw_verify(int m, int Ncols, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, QSym qsym,
-                                          GwU64x2* hist, size_t stride, uint32_t* cig_out, GwVerifyOut* out) {
-    const int w = 64;
-    const int bMax = gw_max(1, (m + w - 1) / w);
-    int D[GW_MAX_NB];
-    int scoreBoundary[GW_MAX_NB];
-    u64 vp[GW_MAX_NB], vn[GW_MAX_NB];  // column j values of the active blocks
+GW_HD void gw_dp_begin(GwDp& d, int m, int Ncols, int band_k, GwU64x2* hist, size_t stride) {
+    d.m = m; d.ncols = Ncols; d.bmax = gw_max(1, (m + 63) / 64); d.j = 0;
 #pragma unroll
-    for (int r = 0; r < GW_MAX_NB; ++r) {
-        D[r] = 0; vp[r] = ~0ULL; vn[r] = 0ULL;
-        scoreBoundary[r] = gw_max(m - ((r + 1) * w) + band_k, 0);
-    }
-    D[0] = m;
-    for (int r = 0; r < bMax; ++r) hist[(size_t)r * stride] = GwU64x2{~0ULL, 0ULL};  // column 0
-    int bCeil = gw_max(1, (band_k + w - 1) / w);
-    if (bCeil > bMax) bCeil = bMax;  // band_k <= 64 in practice; keeps indices in range
-    bool hasBest = false;
-    int bestTail = -1, bestDiff = 0;
-    for (int j = 0; j < Ncols; ++j) {
+    for (int r = 0; r < GW_MAX_NB; ++r) { d.D[r] = 0; d.vp[r] = ~0ULL; d.vn[r] = 0ULL; }
+    d.D[0] = m;
+    for (int r = 0; r < d.bmax; ++r) hist[(size_t)r * stride] = GwU64x2{~0ULL, 0ULL};  // column 0
+    d.bceil = gw_max(1, (band_k + 63) / 64);
+    if (d.bceil > d.bmax) d.bceil = d.bmax;  // band_k <= 64 in practice; keeps indices in range
+    d.has_best = 0; d.best_tail = -1; d.best_diff = 0;
+}
+
+// peq: [4][GW_MAX_NB] pattern masks of the query (bits >= m clear); refsym(j): reference symbol (0..4) of window column j
+template <typename RefSym>
+GW_HD void gw_dp_columns(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, GwU64x2* hist, size_t stride) {
+    const int w = 64;
+    const int m = d.m, bMax = d.bmax;
+    int bCeil = d.bceil;
+    int D[GW_MAX_NB];
+    u64 vp[GW_MAX_NB], vn[GW_MAX_NB];
+#pragma unroll
+    for (int r = 0; r < GW_MAX_NB; ++r) { D[r] = d.D[r]; vp[r] = d.vp[r]; vn[r] = d.vn[r]; }
+    bool hasBest = d.has_best != 0;
+    int bestTail = d.best_tail, bestDiff = d.best_diff;
+    if (jEnd > d.ncols) jEnd = d.ncols;
+    for (int j = d.j; j < jEnd; ++j) {
         const int ch = refsym(j);
         int carry = 0;
         GwU64x2* col = hist + (size_t)(j + 1) * bMax * stride;
@@ -61,49 +74,76 @@ GW_HD void gw_verify(int m, int Ncols, int band_k, const u64 (*peq)[GW_MAX_NB], 
                 carry = hout;
             }
         }
+        // activation of the next block (:425-431) — written without dynamic indexing so that D/vp/vn stay in registers
         bool activated = false;
-        if (bCeil < bMax) {
-            const int r = bCeil;
-            u64 x = ch < 4 ? peq[ch][r] : 0ULL;
-            if (D[r - 1] - carry <= scoreBoundary[r - 1] && (((x & 1ULL) != 0ULL) | (carry < 0))) {
-                // vp[r][j] = ~0, vn[r][j] = 0 ; then one block step
-                hist[((size_t)j * bMax + r) * stride] = GwU64x2{~0ULL, 0ULL};
-                u64 vpr = ~0ULL, vnr = 0ULL;
-                if (carry < 0) x |= 1ULL;
-                u64 d0 = (((x & vpr) + vpr) ^ vpr) | x | vnr;
-                u64 hp = vnr | ~(d0 | vpr);
-                u64 hn = d0 & vpr;
-                int hout = (int)((hp >> 63) & 1ULL) - (int)((hn >> 63) & 1ULL);
-                u64 hp2 = hp << 1, hn2 = hn << 1;
-                if (carry < 0) hn2 |= 1ULL;
-                if (carry > 0) hp2 |= 1ULL;
-                vp[r] = hn2 | ~(d0 | hp2);
-                vn[r] = d0 & hp2;
-                col[(size_t)r * stride] = GwU64x2{vp[r], vn[r]};
-                D[r] = D[r - 1] - carry + hout;
-                bCeil++;
-                computed = bCeil;
-                activated = true;
+#pragma unroll
+        for (int r = 1; r < GW_MAX_NB; ++r) {
+            if (!activated && r == bCeil && r < bMax) {
+                u64 x = ch < 4 ? peq[ch][r] : 0ULL;
+                if (D[r - 1] - carry <= gw_score_boundary(m, band_k, r - 1) && (((x & 1ULL) != 0ULL) | (carry < 0))) {
+                    // vp[r][j] = ~0, vn[r][j] = 0 ; then one block step
+                    hist[((size_t)j * bMax + r) * stride] = GwU64x2{~0ULL, 0ULL};
+                    u64 vpr = ~0ULL, vnr = 0ULL;
+                    if (carry < 0) x |= 1ULL;
+                    u64 d0 = (((x & vpr) + vpr) ^ vpr) | x | vnr;
+                    u64 hp = vnr | ~(d0 | vpr);
+                    u64 hn = d0 & vpr;
+                    int hout = (int)((hp >> 63) & 1ULL) - (int)((hn >> 63) & 1ULL);
+                    u64 hp2 = hp << 1, hn2 = hn << 1;
+                    if (carry < 0) hn2 |= 1ULL;
+                    if (carry > 0) hp2 |= 1ULL;
+                    vp[r] = hn2 | ~(d0 | hp2);
+                    vn[r] = d0 & hp2;
+                    col[(size_t)r * stride] = GwU64x2{vp[r], vn[r]};
+                    D[r] = D[r - 1] - carry + hout;
+                    bCeil = r + 1;
+                    computed = bCeil;
+                    activated = true;
+                }
             }
         }
-        if (!activated) {
-            while (bCeil > 1 && D[bCeil - 1] > scoreBoundary[bCeil - 1] + w) --bCeil;
+        if (!activated) {   // while (bCeil > 1 && D[bCeil - 1] > scoreBoundary[bCeil - 1] + w) --bCeil;  (:439-441)
+#pragma unroll
+            for (int r = GW_MAX_NB - 1; r >= 1; --r)
+                if (bCeil == r + 1 && D[r] > gw_score_boundary(m, band_k, r) + w) bCeil = r;
         }
         // blocks not computed in this step: column j+1 keeps the zero initial value of the Java arrays
         // (a block deactivated just now was computed and keeps its values, as in the reference)
-        for (int r = computed; r < bMax; ++r) col[(size_t)r * stride] = GwU64x2{0ULL, 0ULL};
+#pragma unroll
+        for (int r = 1; r < GW_MAX_NB; ++r)
+            if (r >= computed && r < bMax) col[(size_t)r * stride] = GwU64x2{0ULL, 0ULL};
         if (bCeil == bMax) {
-            if (!hasBest) { hasBest = true; bestTail = j; bestDiff = D[bCeil - 1]; }
-            else if (bestDiff > D[bCeil - 1]) { bestTail = j; bestDiff = D[bCeil - 1]; }
+            int dl = D[0];
+#pragma unroll
+            for (int r = 1; r < GW_MAX_NB; ++r) if (r == bMax - 1) dl = D[r];
+            if (!hasBest) { hasBest = true; bestTail = j; bestDiff = dl; }
+            else if (bestDiff > dl) { bestTail = j; bestDiff = dl; }
         }
     }
+#pragma unroll
+    for (int r = 0; r < GW_MAX_NB; ++r) { d.D[r] = D[r]; d.vp[r] = vp[r]; d.vn[r] = vn[r]; }
+    d.j = jEnd; d.bceil = bCeil; d.has_best = hasBest ? 1 : 0; d.best_tail = bestTail; d.best_diff = bestDiff;
+}
+
+// qsym(i): query symbol (0..4) of row i
+template <typename RefSym, typename QSym>
+GW_HD void gw_dp_traceback(const GwDp& d, RefSym refsym, QSym qsym, const GwU64x2* hist, size_t stride, uint32_t* cig_out, GwVerifyOut* out) {
+    const int m = d.m, bMax = d.bmax;
+    const bool hasBest = d.has_best != 0;
+    const int bestTail = d.best_tail;
     out->cig_overflow = false;
     if (!hasBest) { out->valid = 0; out->pos = 0; out->diff = 0; out->cig_n = 0; return; }
 
     // ---- traceback: ops are produced right-to-left, 2 bits each (0 M, 1 I, 2 D, 3 S)
-    uint32_t ops[(GW_MAX_READ_LEN + GW_MAX_WINDOW + 15) / 16];
+    // 32 ops per word; the word being filled is kept in a register and stored when full
+    u64 ops[(GW_MAX_READ_LEN + GW_MAX_WINDOW + 31) / 32 + 1];
+    u64 acc = 0ULL;
     int nops = 0;
-    auto push = [&](uint32_t op) { ops[nops >> 4] = (nops & 15) ? (ops[nops >> 4] | (op << ((nops & 15) * 2))) : op; ++nops; };
+    auto push = [&](uint32_t op) {
+        acc |= (u64)op << ((nops & 31) * 2);
+        ++nops;
+        if ((nops & 31) == 0) { ops[(nops >> 5) - 1] = acc; acc = 0ULL; }
+    };
     int leftMostPos = 0, diff = 0;
     int col = bestTail, row = m - 1;
     for (;;) {
@@ -125,8 +165,9 @@ GW_HD void gw_verify(int m, int Ncols, int band_k, const u64 (*peq)[GW_MAX_NB], 
             break;
         }
     }
+    ops[nops >> 5] = acc;
     // cigarStr = reverse(ops); strip leading / trailing S,I,D into S (diff-- per I/D)
-    auto opAt = [&](int i) -> uint32_t { int p = nops - 1 - i; return (ops[p >> 4] >> ((p & 15) * 2)) & 3u; };  // i in cigarStr order
+    auto opAt = [&](int i) -> uint32_t { int p = nops - 1 - i; return (uint32_t)(ops[p >> 5] >> ((p & 31) * 2)) & 3u; };  // i in cigarStr order
     int left = 0, right = 0;
     for (int i = 0; i < nops; ++i) {
         uint32_t t = opAt(i);
@@ -158,4 +199,13 @@ GW_HD void gw_verify(int m, int Ncols, int band_k, const u64 (*peq)[GW_MAX_NB], 
     emit(GW_OP_S, (uint32_t)right);
     if (curOp != 0xFFFFFFFFu) { if (n < GW_CIG_CAP) cig_out[n] = (curLen << 4) | curOp; else overflow = true; ++n; }
     out->valid = 1; out->pos = leftMostPos; out->diff = diff; out->cig_n = n < GW_CIG_CAP ? n : GW_CIG_CAP; out->cig_overflow = overflow;
+}
+
+template <typename RefSym, typename QSym>
+GW_HD void gw_verify(int m, int Ncols, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, QSym qsym,
+                                          GwU64x2* hist, size_t stride, uint32_t* cig_out, GwVerifyOut* out) {
+    GwDp d;
+    gw_dp_begin(d, m, Ncols, band_k, hist, stride);
+    gw_dp_columns(d, Ncols, band_k, peq, refsym, hist, stride);
+    gw_dp_traceback(d, refsym, qsym, hist, stride, cig_out, out);
 }

@@ -11,7 +11,7 @@
 #include <vector>
 
 #include "../../include/gw_align.h"
-#include "../../genome_weaver_align_b200/csrc/gw_bodies.cuh"
+#include "../../genome_weaver_align_b200/csrc/gw_fused.cuh"
 #include "../../genome_weaver_align_b200/csrc/gw_host.h"
 #include "../../genome_weaver_align_b200/csrc/gw_image.h"
 
@@ -108,9 +108,21 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
         const uint32_t step_budget = getenv("GWSIM_STEP_BUDGET") ? (uint32_t)atoi(getenv("GWSIM_STEP_BUDGET")) : 0;
         uint32_t max_m = 1;
         for (uint32_t i = 0; i < n_reads; ++i) max_m = std::max<uint32_t>(max_m, (uint32_t)std::min<uint64_t>(offsets[i + 1] - offsets[i], GW_MAX_READ_LEN));
-        std::vector<GwU64x2> hist((size_t)(max_m + 2 * kmax + 2) * ((max_m + 63) / 64));
+        std::vector<GwU64x2> hist((size_t)(max_m + 2 * kmax + 2) * ((max_m + 63) / 64), GwU64x2{0xDEADBEEFDEADBEEFULL, 0xFEEDFACEFEEDFACEULL});   // poison
 
+        const bool fused = !(getenv("GWSIM_ROUNDS") && atoi(getenv("GWSIM_ROUNDS")));
+        GwFusedParams fp;
+        fp.q_lf = getenv("GWSIM_Q_LF") ? atoi(getenv("GWSIM_Q_LF")) : 4;
+        fp.q_cols = getenv("GWSIM_Q_COLS") ? atoi(getenv("GWSIM_Q_COLS")) : 8;
         auto rounds = [&](std::vector<uint32_t> cur) {
+            if (fused) {   // like the fused kernel: every read is driven to completion by one lane, tick by tick
+                for (uint32_t slot : cur) {
+                    GwSlab s(slabs[slot]);
+                    int lp = gw_fused_start(env, s, slot);
+                    while (lp != GW_LP_FETCH) lp = gw_fused_tick(lp, env, s, slot, fp, hist.data(), 1);
+                }
+                return;
+            }
             int flip = 0;
             while (!cur.empty()) {
                 memset(ctr, 0, sizeof(ctr));
@@ -199,7 +211,7 @@ int gwsim_verify_pair(const char* ref, const char* query, int band_k, int* pos, 
         if (c == 4) { for (int a = 0; a < 4; ++a) peq[a][j >> 6] |= 1ULL << (j & 63); }
         else peq[c][j >> 6] |= 1ULL << (j & 63);
     }
-    std::vector<GwU64x2> hist((size_t)(Ncols + 2) * std::max(1, (m + 63) / 64));
+    std::vector<GwU64x2> hist((size_t)(Ncols + 2) * std::max(1, (m + 63) / 64), GwU64x2{0xDEADBEEFDEADBEEFULL, 0xFEEDFACEFEEDFACEULL});   // poison: device scratch is not zeroed
     GwVerifyOut out;
     gw_verify(m, Ncols, band_k, peq, refsym, qsym, hist.data(), 1, cig, &out);
     *pos = out.pos; *nm = out.diff; *cig_n = out.cig_n;
