@@ -19,7 +19,7 @@ GW_HD int gw_q_symbol(const GwReadCtx* c, int strand, int i) {
 }
 
 // reportAlignment request side: classify the fragments of the chain headed by `base`; returns true if the read must park
-GW_HD bool gw_begin_report(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, int32_t base,
+GW_COLD bool gw_begin_report(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, int32_t base,
                                                 const GwRoundQueues& rq) {
     GwReadCtx* c = s.ctx();
     c->pend_base = base;
@@ -50,7 +50,7 @@ GW_HD bool gw_begin_report(const GwSearchEnv& env, const GwSlab& s, uint32_t slo
 }
 
 // reportAlignment completion: ReadHits from the verified fragments, sortSplits, AlignmentResultHolder.add
-GW_HD void gw_finish_report(const GwSearchEnv& env, const GwSlab& s) {
+GW_COLD void gw_finish_report(const GwSearchEnv& env, const GwSlab& s) {
     GwReadCtx* c = s.ctx();
     const int k = c->k;
     int32_t hits[2] = {-1, -1};
@@ -124,7 +124,7 @@ GW_HD const u64* gw_staircase_for(const GwSearchEnv& env, GwReadCtx* c, int* kk)
 #define GW_STEP_DONE 2
 
 // returns GW_STEP_CONTINUE when the read is in the best-first loop and wants gw_step_read calls
-GW_HD int gw_resume_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
+GW_COLD int gw_resume_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
     GwReadCtx* c = s.ctx();
     const int m = c->m, k = c->k;
     const GwDevConfig& cfg = env.cfg;
@@ -184,20 +184,31 @@ GW_HD void gw_yield_read(const GwSlab& s, uint32_t slot, const GwRoundQueues& rq
     rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
 }
 
-// one iteration of the best-first loop. The polled state is copied to registers once; all candidate extensions (the read's own
-// base first, then A,C,G,T) go through ONE FM step + NFA step + insertion site, which keeps the kernel small and lets the lanes
-// of a warp that are in the same loop trip run together.
-GW_HD int gw_step_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
+// One iteration of the best-first loop is cut in two kinds of slices so that the lanes of a warp run the expensive part together:
+//   gw_search_poll   poll the queue, hit test / cut-offs (:352-409); leaves the lane "mid step" when there are candidates to try
+//   gw_search_try    ONE candidate extension = one FM step + one NFA step + one queue insertion (:415-455); the candidates of a
+//                    step (the read's own base first, then A,C,G,T) are tried by consecutive calls; after the last one the
+//                    split / soft-clip children are generated (:457-474)
+// Which candidates are done is recorded in the checked-base flags of the state itself (SearchState.state bits 0-4), exactly where
+// the reference keeps them, so a lane only carries the two arena offsets below between slices.
+struct GwSearchLane {
+    int32_t base;    // polled queue entry (head of the split chain)
+    int32_t c_off;   // fragment of the chain that is being extended
+    int32_t mid;     // 1: candidates of the current step remain
+};
+
+GW_HD int gw_search_poll(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq, GwSearchLane& L) {
     GwReadCtx* c = s.ctx();
-    const int m = c->m, k = c->k;
+    const int m = c->m;
     const GwDevConfig& cfg = env.cfg;
+    L.mid = 0;
     if (c->qn <= 0 || c->n_fm > m * 20) { c->phase = GW_PH_DONE; return GW_STEP_DONE; }   // queue empty / fmIndexSearchUpperBound
     const int32_t base = gw_queue_poll(s, cfg);
     int32_t c_off = base;
-    GwState C = gw_load_state(s, base);
+    const GwState* C = gw_st(s, base);
     for (;;) {   // first fragment of the chain that still has bases to process (:366-379)
-        if (!(gw_has_hit(&C) || gw_is_clipped(&C) || gw_remaining(&C) == 0)) break;
-        if (C.next_split < 0) {
+        if (!(gw_has_hit(C) || gw_is_clipped(C) || gw_remaining(C) == 0)) break;
+        if (C->next_split < 0) {
             if (gw_begin_report(env, s, slot, base, rq)) {
                 c->phase = GW_PH_WAIT_VERIFY;
                 if (rq.counters) rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
@@ -206,55 +217,32 @@ GW_HD int gw_step_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, c
             gw_finish_report(env, s);
             return c->phase == GW_PH_DONE ? GW_STEP_DONE : GW_STEP_CONTINUE;
         }
-        c_off = C.next_split;
-        C = gw_load_state(s, c_off);
+        c_off = C->next_split;
+        C = gw_st(s, c_off);
     }
-    if (gw_is_finished(&C)) return GW_STEP_CONTINUE;
-    const int nm = gw_lower_k(&C);
+    if (gw_is_finished(C)) return GW_STEP_CONTINUE;
+    const int nm = gw_lower_k(C);
     if (nm > c->min_mm) { c->n_cut++; return GW_STEP_CONTINUE; }
-    if (c->min_mm - nm < 0) return GW_STEP_CONTINUE;
     {
         const int scoreUB = gw_score(s, cfg, gw_st(s, base), true);
         if (scoreUB < 0 || scoreUB < c->best_score) { c->n_cut++; return GW_STEP_CONTINUE; }
     }
-    const int strand = gw_strand(&C);
-    const int nextBase = gw_q_symbol(c, strand, gw_next_index(&C));
     // the staircase filter of the current minMismatches is needed on every path from here (:425, :439); where the reference's
     // constructor throws, the read ends here whichever path asked for it
     int kk;
-    const u64* tbl = gw_staircase_for(env, c, &kk);
-    if (!tbl) return GW_STEP_DONE;
-    u64 prev[GW_MAX_ROWS];
-    {
-        const u64* rows = gw_rows(gw_st(s, c_off));
-        for (int i = 0; i < C.height; ++i) prev[i] = rows[i];
-    }
-    int flags = C.state;
-    bool extended = false;   // the read's own base went through: the parent is dropped (:426-429)
-    int fail_status = 0;
-#pragma unroll 1
-    for (int t = 0; t < 5; ++t) {
-        const int ch = t == 0 ? nextBase : t - 1;
-        if ((flags >> ch) & 1) continue;
-        flags |= 1 << ch;
-        if (gw_si_is_empty(&C, ch)) continue;
-        GwSiSet nsi;
-        gw_next_si(env.ix, &C, ch, &nsi, &c->occ_search);
-        c->n_fm++;
-        const int32_t ns = gw_next_state(s, C, prev, ch, nsi, tbl, kk);
-        if (ns == -2) { fail_status = GW_ST_OVERFLOW; break; }
-        if (ns >= 0) {
-            if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { fail_status = GW_ST_OVERFLOW; break; }
-            if (t == 0) { extended = true; break; }
-        } else
-            c->n_filt++;
-    }
-    if (!extended) flags |= 1 << 4;
-    gw_st(s, c_off)->state = flags;   // checked-base flags live on the (possibly shared) state object
-    if (fail_status) { gw_fail(c, fail_status); return GW_STEP_DONE; }
-    if (extended) return GW_STEP_CONTINUE;
-    C.state = flags;
-    if (gw_num_split(s, gw_st(s, base)) < cfg.num_split_allowed && nm + 1 <= c->min_mm) {
+    if (!gw_staircase_for(env, c, &kk)) return GW_STEP_DONE;
+    L.base = base; L.c_off = c_off; L.mid = 1;
+    return GW_STEP_CONTINUE;
+}
+
+// split / soft-clip children of the state whose candidates are exhausted (:457-474)
+GW_COLD int gw_search_split(const GwSearchEnv& env, const GwSlab& s, const GwSearchLane& L) {
+    GwReadCtx* c = s.ctx();
+    const int m = c->m, k = c->k;
+    const GwDevConfig& cfg = env.cfg;
+    const GwState C = gw_load_state(s, L.c_off);
+    const int nm = gw_lower_k(&C);
+    if (gw_num_split(s, gw_st(s, L.base)) < cfg.num_split_allowed && nm + 1 <= c->min_mm) {
         const int index = gw_next_index(&C);
         if (index > cfg.indel_end_skip && m - index >= cfg.indel_end_skip) {
 #pragma unroll 1
@@ -262,12 +250,71 @@ GW_HD int gw_step_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, c
                 const int32_t ns = gw_split_state(env, s, C, k, clip != 0);
                 if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
                 if (ns == -3) { gw_fail(c, GW_ST_ABORT); return GW_STEP_DONE; }
-                if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
+                if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, L.base, L.c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
                 else if (clip == 0) c->n_filt++;
             }
         }
     }
     return GW_STEP_CONTINUE;
+}
+
+GW_HD int gw_search_try(const GwSearchEnv& env, const GwSlab& s, GwSearchLane& L) {
+    GwReadCtx* c = s.ctx();
+    const GwDevConfig& cfg = env.cfg;
+    GwState* Cp = gw_st(s, L.c_off);
+    const GwState C = *Cp;
+    const int strand = gw_strand(&C);
+    const int nextBase = gw_q_symbol(c, strand, gw_next_index(&C));
+    int flags = C.state;
+    // next candidate in the reference's order: the read's own base, then A,C,G,T; checked or empty ones are passed over (and
+    // marked checked) (:415-455). Written without branches so that the lanes of a warp stay together up to the FM step.
+    int viable = 0;
+#pragma unroll
+    for (int cand = 0; cand < 4; ++cand)
+        if (!((flags >> cand) & 1) && !gw_si_is_empty(&C, cand)) viable |= 1 << cand;
+    const bool own = ((viable >> nextBase) & 1) != 0;
+    int ch;
+    if (own) { ch = nextBase; flags |= 1 << nextBase; }
+    else if (viable) {
+        ch = 0;
+#pragma unroll
+        for (int cand = 3; cand >= 0; --cand) if ((viable >> cand) & 1) ch = cand;
+        flags |= ((2 << ch) - 1) | (1 << nextBase);
+    } else { ch = -1; flags |= 0xF; }
+    if (ch < 0) {   // candidates exhausted without extending with the read's own base
+        flags |= 1 << 4;
+        Cp->state = flags;
+        L.mid = 0;
+        return gw_search_split(env, s, L);
+    }
+    int kk;
+    const u64* tbl = gw_staircase_for(env, c, &kk);
+    u64 prev[GW_MAX_ROWS];
+    {
+        const u64* rows = gw_rows(Cp);
+        for (int i = 0; i < C.height; ++i) prev[i] = rows[i];
+    }
+    GwSiSet nsi;
+    gw_next_si(env.ix, &C, ch, &nsi, &c->occ_search);
+    c->n_fm++;
+    const int32_t ns = gw_next_state(s, C, prev, ch, nsi, tbl, kk);
+    if (ns == -2) { Cp->state = flags; gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+    if (ns >= 0) {
+        if (!gw_queue_add(s, cfg, gw_update(s, L.base, L.c_off, ns))) { Cp->state = flags; gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+        if (own) { Cp->state = flags; L.mid = 0; return GW_STEP_CONTINUE; }   // extended: the parent is dropped (:426-429)
+    } else
+        c->n_filt++;
+    Cp->state = flags;
+    return GW_STEP_CONTINUE;
+}
+
+// one whole iteration of the best-first loop (sequential form: the round-based search kernel and the host simulator)
+GW_HD int gw_step_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
+    GwSearchLane L;
+    int r = gw_search_poll(env, s, slot, rq, L);
+#pragma unroll 1
+    while (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try(env, s, L);
+    return r;
 }
 
 // Runs one read until it finishes or parks (sequential form of the two functions above).

@@ -19,8 +19,12 @@
 
 #if defined(__CUDACC__)
 #define GW_HD __host__ __device__ __forceinline__
+// rarely executed, large bodies (seeding, reporting, split states, DP set-up, traceback): ONE out-of-line copy keeps the hot loops
+// of the fused kernel small enough for the instruction cache
+#define GW_COLD static __host__ __device__ __noinline__
 #else
 #define GW_HD inline
+#define GW_COLD static inline
 #endif
 
 typedef unsigned long long u64;

@@ -16,6 +16,7 @@
 
 struct GwFusedParams {
     int32_t q_lf, q_cols;
+    int32_t stick;   // a warp keeps running its current kind of slice while 16 * (largest group) <= stick * (current group)
 };
 
 GW_HD GwRoundQueues gw_no_queues() {
@@ -25,7 +26,7 @@ GW_HD GwRoundQueues gw_no_queues() {
 }
 
 // picks the next pending fragment that needs locate (+ verify), or resumes the automaton with the results
-GW_HD int gw_job_next(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, int from_frag) {
+GW_COLD int gw_job_next(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, int from_frag) {
     GwReadCtx* c = s.ctx();
     for (;;) {
         for (int f = from_frag; f < c->pend_n; ++f) {
@@ -49,9 +50,14 @@ GW_HD int gw_fused_start(const GwSearchEnv& env, const GwSlab& s, uint32_t slot)
     return gw_job_next(env, s, slot, 0);
 }
 
-GW_HD int gw_fused_search_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t slot) {
-    const int r = gw_step_read(env, s, slot, gw_no_queues());
+// search slice: (poll the queue unless the lane is in the middle of a step) + ONE candidate extension. All searching lanes of a warp
+// pass through the two sections together, whatever number of candidates their current step needs.
+GW_HD int gw_fused_search_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, GwSearchLane& L) {
+    int r = GW_STEP_CONTINUE;
+    if (!L.mid) r = gw_search_poll(env, s, slot, gw_no_queues(), L);
+    if (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try(env, s, L);
     if (r == GW_STEP_CONTINUE) return GW_LP_SEARCH;
+    L.mid = 0;
     if (r == GW_STEP_DONE) return GW_LP_FETCH;
     return gw_job_next(env, s, slot, 0);
 }
@@ -66,10 +72,10 @@ GW_HD u64 gw_plane_window(const u64* plane, uint32_t n_words, uint32_t p) {
 }
 
 // AlignmentProcess.verify, window + query set-up (:517-538); returns false when the fragment is finished without a DP
-GW_HD bool gw_job_begin_dp(const GwSearchEnv& env, const GwSlab& s, GwU64x2* hist, size_t stride) {
+GW_COLD bool gw_job_begin_dp(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag, GwU64x2* hist, size_t stride) {
     GwReadCtx* c = s.ctx();
-    GwJob* job = &c->job;
-    GwPendFrag* pf = &c->pend[job->frag];
+    job->frag = frag;
+    GwPendFrag* pf = &c->pend[frag];
     const GwIndexView& ix = env.ix;
     const GwState* st = gw_st(s, pf->state_off);
     const int strand = gw_strand(st);
@@ -84,6 +90,9 @@ GW_HD bool gw_job_begin_dp(const GwSearchEnv& env, const GwSlab& s, GwU64x2* his
     pf->res_abort = 0;
     if (refStart > refEnd) { pf->res_abort = 1; pf->res_valid = 0; return false; }  // ACGTSequence.subString throws
     const int Ncols = (int)(refEnd - refStart);
+#ifdef GW_VERIFY_STATS
+    fprintf(stderr, "VS %d %d %d %d %lld %d\n", c->read_id, strand, start, end, refStart, Ncols);
+#endif
     // pattern masks of the fragment q[strand][start, end), reversed on the reverse strand (:529-534), from the read's bit planes
     const int m = c->m;
     const int nbf = gw_max(1, (fragLen + 63) >> 6);
@@ -136,43 +145,75 @@ GW_HD int gw_fused_locate_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t
     pf->textpos = j == 0 ? smp : (uint32_t)(((u64)smp + (u64)j + ix.N) % ix.N);
     c->occ_locate += (uint32_t)j;
     if (c->phase == GW_PH_WAIT_EXACT) return gw_job_next(env, s, slot, c->pend_n);   // exact hit: no verification (:490-494)
-    if (gw_job_begin_dp(env, s, hist, stride)) return GW_LP_DP;
+    if (gw_job_begin_dp(env, s, job, job->frag, hist, stride)) return GW_LP_DP;
     return gw_job_next(env, s, slot, job->frag + 1);
 }
 
-GW_HD int gw_fused_dp_tick(const GwSearchEnv& env, const GwSlab& s, const GwFusedParams& fp, GwU64x2* hist, size_t stride) {
-    GwJob* job = &s.ctx()->job;
-    GwDp d = job->dp;
-    auto refsym = [&](int j) -> int { return gw_job_ref_symbol(job, j); };
-    gw_dp_columns(d, d.j + fp.q_cols, env.cfg.band_width, job->peq, refsym, hist, stride);
-    job->dp = d;
-    return d.j >= d.ncols ? GW_LP_TRACE : GW_LP_DP;
-}
-
-GW_HD int gw_fused_trace_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, GwU64x2* hist, size_t stride) {
+// traceback + CIGAR of the fragment whose DP is complete; results go to its pending-fragment record
+GW_HD void gw_job_trace(const GwSlab& s, GwJob* job, const GwU64x2* hist, size_t stride) {
     GwReadCtx* c = s.ctx();
-    GwJob* job = &c->job;
     GwPendFrag* pf = &c->pend[job->frag];
     const GwState* st = gw_st(s, pf->state_off);
     const int strand = gw_strand(st), start = st->start, end = st->end;
     const u64* qlo = c->qlo[strand];
     const u64* qhi = c->qhi[strand];
+    // the traceback moves through rows and columns one at a time: keep the 64-symbol words it is in
+    int qw = -1; u64 ql = 0, qh = 0;
     auto qsym = [&](int i) -> int {
         const int p = strand == 0 ? start + i : end - 1 - i;
-        return (int)((((qhi[p >> 6] >> (p & 63)) & 1ULL) << 1) | ((qlo[p >> 6] >> (p & 63)) & 1ULL));
+        if ((p >> 6) != qw) { qw = p >> 6; ql = qlo[qw]; qh = qhi[qw]; }
+        return (int)((((qh >> (p & 63)) & 1ULL) << 1) | ((ql >> (p & 63)) & 1ULL));
     };
-    auto refsym = [&](int j) -> int { return gw_job_ref_symbol(job, j); };
+    int rw = -1; u64 rl = 0, rh = 0, rn = 0;
+    auto refsym = [&](int j) -> int {
+        if ((j >> 6) != rw) { rw = j >> 6; rl = job->rw_lo[rw]; rh = job->rw_hi[rw]; rn = job->rw_nf[rw]; }
+        const int sft = j & 63;
+        if ((rn >> sft) & 1ULL) return 4;
+        return (int)((((rh >> sft) & 1ULL) << 1) | ((rl >> sft) & 1ULL));
+    };
     GwVerifyOut out;
     gw_dp_traceback(job->dp, refsym, qsym, hist, stride, pf->cig, &out);
     pf->res_valid = out.valid; pf->res_pos = out.pos; pf->res_diff = out.diff; pf->res_cig_n = out.cig_n;
     if (out.cig_overflow) pf->res_abort = 2;  // cannot happen within GW_MAX_K; reported as unsupported
+}
+
+GW_COLD int gw_fused_trace_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, GwU64x2* hist, size_t stride) {
+    GwJob* job = &s.ctx()->job;
+    gw_job_trace(s, job, hist, stride);
     return gw_job_next(env, s, slot, job->frag + 1);
 }
 
+// DP columns [d.j, jEnd) of a job
+GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int n_cols, GwU64x2* hist, size_t stride) {
+    GwDp d = job->dp;
+    int rw = -1; u64 rl = 0, rh = 0, rn = 0;
+    auto refsym = [&](int j) -> int {   // columns advance one by one: reload the window words every 64 columns only
+        if ((j >> 6) != rw) { rw = j >> 6; rl = job->rw_lo[rw]; rh = job->rw_hi[rw]; rn = job->rw_nf[rw]; }
+        const int sft = j & 63;
+        if ((rn >> sft) & 1ULL) return 4;
+        return (int)((((rh >> sft) & 1ULL) << 1) | ((rl >> sft) & 1ULL));
+    };
+    gw_dp_columns(d, d.j + n_cols, env.cfg.band_width, job->peq, refsym, hist, stride);
+    job->dp = d;
+}
+
+// whole verification of one pending fragment in one go (pool kernel: the job lives in the lane's local memory)
+GW_HD void gw_verify_frag(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag, GwU64x2* hist, size_t stride) {
+    if (!gw_job_begin_dp(env, s, job, frag, hist, stride)) return;
+    gw_job_columns(env, job, job->dp.ncols, hist, stride);
+    gw_job_trace(s, job, hist, stride);
+}
+
+GW_HD int gw_fused_dp_tick(const GwSearchEnv& env, const GwSlab& s, const GwFusedParams& fp, GwU64x2* hist, size_t stride) {
+    GwJob* job = &s.ctx()->job;
+    gw_job_columns(env, job, fp.q_cols, hist, stride);
+    return job->dp.j >= job->dp.ncols ? GW_LP_TRACE : GW_LP_DP;
+}
+
 // one tick of whatever the lane is doing; returns the lane's next state
-GW_HD int gw_fused_tick(int lp, const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwFusedParams& fp, GwU64x2* hist, size_t stride) {
+GW_HD int gw_fused_tick(int lp, const GwSearchEnv& env, const GwSlab& s, uint32_t slot, GwSearchLane& L, const GwFusedParams& fp, GwU64x2* hist, size_t stride) {
     switch (lp) {
-    case GW_LP_SEARCH: return gw_fused_search_tick(env, s, slot);
+    case GW_LP_SEARCH: return gw_fused_search_tick(env, s, slot, L);
     case GW_LP_LOCATE: return gw_fused_locate_tick(env, s, slot, fp, hist, stride);
     case GW_LP_DP: return gw_fused_dp_tick(env, s, fp, hist, stride);
     case GW_LP_TRACE: return gw_fused_trace_tick(env, s, slot, hist, stride);

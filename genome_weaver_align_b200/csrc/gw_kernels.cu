@@ -129,14 +129,17 @@ __global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_search_kernel(GwSearchEn
 // verification. Per trip of the warp loop the lanes that search run one best-first iteration, those locating run a few LF
 // steps, those verifying a slice of DP columns; a lane whose read is finished takes the next one from the work list.
 __global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_fused_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
-                                                                     uint32_t* work_counter, GwU64x2* hist, GwFusedParams fp) {
+                                                                     uint32_t* work_counter, GwU64x2* hist, GwFusedParams fp, const uint32_t* n_active_dev) {
     const unsigned full = 0xFFFFFFFFu;
+    if (n_active_dev) n_active = *n_active_dev;   // list length produced on the device (leftovers of the pool kernel)
     const unsigned lane = threadIdx.x & 31u;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int lp = GW_LP_FETCH;
+    int lp = GW_LP_FETCH, mode = GW_LP_SEARCH;
     bool exhausted = false;
     GwSlab s;
+    GwSearchLane L;
+    L.base = L.c_off = -1; L.mid = 0;
     uint32_t slot = 0;
     for (;;) {
         const unsigned need = __ballot_sync(full, lp == GW_LP_FETCH && !exhausted);
@@ -150,19 +153,173 @@ __global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_fused_kernel(GwSearchEnv
                 if (idx < n_active) {
                     slot = active ? active[idx] : idx;
                     s = GwSlab(slabs[slot]);
+                    L.mid = 0;
                     lp = gw_fused_start(env, s, slot);
                 } else
                     exhausted = true;
             }
         }
-        if (!__any_sync(full, lp != GW_LP_FETCH)) {
+        // The warp runs ONE kind of slice per trip — the kind most of its lanes are waiting for — so the lanes that execute
+        // together follow the same code; lanes in another stage wait until their stage has the majority (or the current one
+        // has drained). `mode` is warp-uniform, so the dispatch below does not diverge.
+        const int cS = __popc(__ballot_sync(full, lp == GW_LP_SEARCH)), cL = __popc(__ballot_sync(full, lp == GW_LP_LOCATE));
+        const int cD = __popc(__ballot_sync(full, lp == GW_LP_DP)), cT = __popc(__ballot_sync(full, lp == GW_LP_TRACE));
+        if (cS + cL + cD + cT == 0) {
             if (__all_sync(full, exhausted)) break;
             continue;
         }
-        if (lp == GW_LP_SEARCH) lp = gw_fused_search_tick(env, s, slot);
-        else if (lp == GW_LP_LOCATE) lp = gw_fused_locate_tick(env, s, slot, fp, my_hist, stride);
-        else if (lp == GW_LP_DP) lp = gw_fused_dp_tick(env, s, fp, my_hist, stride);
-        else if (lp == GW_LP_TRACE) lp = gw_fused_trace_tick(env, s, slot, my_hist, stride);
+        int best = cS, bm = GW_LP_SEARCH;
+        if (cL > best) { best = cL; bm = GW_LP_LOCATE; }
+        if (cD > best) { best = cD; bm = GW_LP_DP; }
+        if (cT > best) { best = cT; bm = GW_LP_TRACE; }
+        const int cur = mode == GW_LP_SEARCH ? cS : mode == GW_LP_LOCATE ? cL : mode == GW_LP_DP ? cD : mode == GW_LP_TRACE ? cT : 0;
+        if (cur * fp.stick < best * 16 || cur == 0) mode = bm;   // leave the current kind of slice only for a clearly larger group
+        if (mode == GW_LP_SEARCH) { if (lp == GW_LP_SEARCH) lp = gw_fused_search_tick(env, s, slot, L); }
+        else if (mode == GW_LP_LOCATE) { if (lp == GW_LP_LOCATE) lp = gw_fused_locate_tick(env, s, slot, fp, my_hist, stride); }
+        else if (mode == GW_LP_DP) { if (lp == GW_LP_DP) lp = gw_fused_dp_tick(env, s, fp, my_hist, stride); }
+        else { if (lp == GW_LP_TRACE) lp = gw_fused_trace_tick(env, s, slot, my_hist, stride); }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Block-level pool: a CTA keeps up to GW_POOL reads in flight and advances them in three phases separated by CTA barriers —
+//   S  search slices for the reads that can search (lanes take reads from a shared list; a read that needs verification, or
+//      that used up its step budget, goes to the next round's list),
+//   L  SA locate of the fragments waiting for verification (one LF walk per fragment),
+//   D  bit-vector DP + traceback of those fragments —
+// so that the lanes running together always execute the same kind of work, without device-wide rounds: CTAs are not
+// synchronised with each other and refill their pool from the global work list as reads finish. When the work list is
+// drained and a pool has shrunk below `tail_thr` reads, the CTA hands its remaining reads to the leftover list (they are
+// finished by gw_fused_kernel, whose lanes are independent).
+#define GW_POOL_THREADS 256
+#define GW_POOL 1024
+
+struct GwPoolParams {
+    uint32_t budget;     // search slices per read and round
+    uint32_t tail_thr;   // pool size below which the CTA hands over
+};
+
+__global__ void __launch_bounds__(GW_POOL_THREADS) gw_pool_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
+                                                                  uint32_t* work_counter, GwU64x2* hist, GwPoolParams pp, uint32_t* leftover,
+                                                                  uint32_t* leftover_count) {
+    __shared__ uint32_t ready[2][GW_POOL];       // reads to resume / continue, this round and the next
+    __shared__ uint32_t frags[2 * GW_POOL];      // slot * 2 + fragment waiting for locate (+ verify)
+    __shared__ uint32_t n_ready[2], n_frags, head, pool, drained, cur, refill_first, refill_base, refill_n, lo_base;
+    const uint32_t tid = threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + tid;
+    const GwRoundQueues noq = gw_no_queues();
+    if (tid == 0) { n_ready[0] = n_ready[1] = 0; n_frags = 0; pool = 0; drained = 0; cur = 0; }
+    __syncthreads();
+    for (;;) {
+        // ---- refill the pool from the global work list
+        if (tid == 0) {
+            head = 0; refill_n = 0;
+            n_ready[cur ^ 1] = 0; n_frags = 0;
+            if (!drained && pool < GW_POOL) {
+                const uint32_t want = GW_POOL - pool;
+                const uint32_t first = atomicAdd(work_counter, want);
+                uint32_t got = 0;
+                if (first < n_active) got = min(want, n_active - first);
+                if (first + want >= n_active) drained = 1;
+                refill_first = first; refill_base = n_ready[cur]; refill_n = got;
+                n_ready[cur] += got; pool += got;
+            }
+        }
+        __syncthreads();
+        for (uint32_t i = tid; i < refill_n; i += blockDim.x) ready[cur][refill_base + i] = active ? active[refill_first + i] : refill_first + i;
+        const uint32_t c_idx = cur, n_idx = cur ^ 1u;
+        const uint32_t nr = n_ready[c_idx];
+        if (pool == 0) break;
+        if (drained && pool < pp.tail_thr) {   // hand the stragglers over
+            if (tid == 0) lo_base = atomicAdd(leftover_count, nr);
+            __syncthreads();
+            for (uint32_t i = tid; i < nr; i += blockDim.x) leftover[lo_base + i] = ready[c_idx][i];
+            break;
+        }
+        __syncthreads();
+        // ---- phase S
+        {
+            bool have = false;
+            GwSlab s;
+            GwSearchLane L;
+            L.base = L.c_off = -1; L.mid = 0;
+            uint32_t slot = 0, budget = 0;
+            for (;;) {
+                if (!have) {
+                    const uint32_t i = atomicAdd(&head, 1u);
+                    if (i >= nr) break;
+                    slot = ready[c_idx][i];
+                    s = GwSlab(slabs[slot]);
+                    L.mid = 0;
+                    budget = pp.budget;
+                    const int r0 = gw_resume_read(env, s, slot, noq);
+                    if (r0 == GW_STEP_DONE) { atomicSub(&pool, 1u); continue; }
+                    if (r0 == GW_STEP_PARKED) {   // exact hit: needs its locate only
+                        ready[n_idx][atomicAdd(&n_ready[n_idx], 1u)] = slot;
+                        frags[atomicAdd(&n_frags, 1u)] = slot * 2u;
+                        continue;
+                    }
+                    have = true;
+                }
+                int r = GW_STEP_CONTINUE;
+                if (!L.mid) r = gw_search_poll(env, s, slot, noq, L);
+                if (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try(env, s, L);
+                if (r == GW_STEP_CONTINUE) {
+                    if (--budget == 0 && !L.mid) { ready[n_idx][atomicAdd(&n_ready[n_idx], 1u)] = slot; have = false; }
+                    else if (budget == 0) budget = 1;   // finish the step that is under way
+                } else if (r == GW_STEP_DONE) { atomicSub(&pool, 1u); have = false; }
+                else {   // parked with a verification request
+                    const GwReadCtx* c = s.ctx();
+                    ready[n_idx][atomicAdd(&n_ready[n_idx], 1u)] = slot;
+                    for (int f = 0; f < c->pend_n; ++f)
+                        if (c->pend[f].kind == 2) frags[atomicAdd(&n_frags, 1u)] = slot * 2u + (uint32_t)f;
+                    have = false;
+                }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) head = 0;
+        __syncthreads();
+        const uint32_t nf = n_frags;
+        // ---- phase L: lanes stay in the LF loop and take the next fragment when their walk ends
+        {
+            bool have = false;
+            GwPendFrag* pf = nullptr;
+            GwReadCtx* c = nullptr;
+            uint32_t cursor = 0;
+            int j = 0, fm = 0;
+            for (;;) {
+                if (!have) {
+                    const uint32_t i = atomicAdd(&head, 1u);
+                    if (i >= nf) break;
+                    const uint32_t id = frags[i];
+                    c = reinterpret_cast<GwReadCtx*>(slabs[id >> 1]);
+                    pf = &c->pend[id & 1u];
+                    cursor = pf->sa_index; fm = pf->fm; j = 0;
+                    have = true;
+                }
+                if ((cursor % GW_SSA_L) != 0) { cursor = gw_suffix_link(env.ix, fm, cursor); ++j; }
+                if ((cursor % GW_SSA_L) == 0) {
+                    const uint32_t smp = gw_ld32(env.ix.ssa[fm] + cursor / GW_SSA_L);
+                    pf->textpos = j == 0 ? smp : (uint32_t)(((u64)smp + (u64)j + env.ix.N) % env.ix.N);
+                    atomicAdd(&c->occ_locate, (uint32_t)j);   // the two fragments of a read may be walked by different lanes
+                    have = false;
+                }
+            }
+        }
+        __syncthreads();
+        // ---- phase D
+        for (uint32_t i = tid; i < nf; i += blockDim.x) {
+            const uint32_t id = frags[i];
+            GwSlab s(slabs[id >> 1]);
+            if (s.ctx()->phase == GW_PH_WAIT_EXACT) continue;   // exact hit: no verification (:490-494)
+            GwJob job;
+            gw_verify_frag(env, s, &job, (int)(id & 1u), my_hist, stride);
+        }
+        __syncthreads();
+        if (tid == 0) cur = n_idx;
+        __syncthreads();
     }
 }
 
@@ -319,11 +476,18 @@ void gwk_search(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, cons
     gw_search_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, rq, work_counter, tail_steps);
 }
 void gwk_fused(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-               int q_lf, int q_cols, uint32_t blocks) {
+               int q_lf, int q_cols, int stick, uint32_t blocks, const uint32_t* n_active_dev) {
     if (!n_active) return;
     GwFusedParams fp;
-    fp.q_lf = q_lf; fp.q_cols = q_cols;
-    gw_fused_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, fp);
+    fp.q_lf = q_lf; fp.q_cols = q_cols; fp.stick = stick;
+    gw_fused_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, fp, n_active_dev);
+}
+void gwk_pool(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
+              uint32_t budget, uint32_t tail_thr, uint32_t blocks, uint32_t* leftover, uint32_t* leftover_count) {
+    if (!n_active) return;
+    GwPoolParams pp;
+    pp.budget = budget; pp.tail_thr = tail_thr;
+    gw_pool_kernel<<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
 }
 void gwk_locate(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
     if (n) gw_locate_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, slabs, req, n);

@@ -263,7 +263,7 @@ GW_HD int32_t gw_next_state(const GwSlab& s, const GwState& c, const u64* prev, 
 
 // SearchState.nextStateAfterSplit (clip == false) / nextStateAfterClipping (clip == true) on a register copy of the current
 // state; -1 null, -2 overflow, -3 abort
-GW_HD int32_t gw_split_state(const GwSearchEnv& env, const GwSlab& s, const GwState& c, int k, bool clip) {
+GW_COLD int32_t gw_split_state(const GwSearchEnv& env, const GwSlab& s, const GwState& c, int k, bool clip) {
     const int minK = gw_lower_k(&c);
     if (!(minK < k)) return -1;
     const int newHeight = (int)c.height - 1;

@@ -8,6 +8,8 @@
 #pragma once
 #include "gw_fm.cuh"
 
+#define GW_RUN_CAP 64   // run-length encoded traceback ops kept per fragment (>= 2 * GW_MAX_K + 3)
+
 struct GwVerifyOut {
     int valid;   // 0: reference returns null
     int pos, diff, cig_n;
@@ -134,70 +136,68 @@ GW_HD void gw_dp_traceback(const GwDp& d, RefSym refsym, QSym qsym, const GwU64x
     out->cig_overflow = false;
     if (!hasBest) { out->valid = 0; out->pos = 0; out->diff = 0; out->cig_n = 0; return; }
 
-    // ---- traceback: ops are produced right-to-left, 2 bits each (0 M, 1 I, 2 D, 3 S)
-    // 32 ops per word; the word being filled is kept in a register and stored when full
-    u64 ops[(GW_MAX_READ_LEN + GW_MAX_WINDOW + 31) / 32 + 1];
-    u64 acc = 0ULL;
-    int nops = 0;
+    // ---- traceback: ops (0 M, 1 I, 2 D, 3 S) are produced right-to-left and run-length encoded on the fly
+    uint32_t runs[GW_RUN_CAP];   // len << 2 | op, right-most run first
+    int nruns = 0;
+    uint32_t curOp = 4u, curLen = 0u;
     auto push = [&](uint32_t op) {
-        acc |= (u64)op << ((nops & 31) * 2);
-        ++nops;
-        if ((nops & 31) == 0) { ops[(nops >> 5) - 1] = acc; acc = 0ULL; }
+        if (op == curOp) { ++curLen; return; }
+        if (curLen) { if (nruns < GW_RUN_CAP) runs[nruns] = (curLen << 2) | curOp; ++nruns; }
+        curOp = op; curLen = 1u;
     };
     int leftMostPos = 0, diff = 0;
     int col = bestTail, row = m - 1;
+    int hcol = -2, hblk = -1;
+    GwU64x2 v = GwU64x2{0ULL, 0ULL};
     for (;;) {
         int path = 0;
         if (col >= 0 && row >= 0) {
-            int block = row >> 6, offset = row & 63;
-            GwU64x2 v = hist[((size_t)(col + 1) * bMax + block) * stride];
-            bool vpf = (v.x >> offset) & 1ULL, vnf = (v.y >> offset) & 1ULL;
+            const int block = row >> 6, offset = row & 63;
+            if (col != hcol || block != hblk) { v = hist[((size_t)(col + 1) * bMax + block) * stride]; hcol = col; hblk = block; }
             if (refsym(col) == qsym(row)) path = 1;
-            else if (vpf) { path = 3; diff++; }
-            else if (!vnf) { path = 2; diff++; }
+            else if ((v.x >> offset) & 1ULL) { path = 3; diff++; }
+            else if (!((v.y >> offset) & 1ULL)) { path = 2; diff++; }
             else { path = 4; diff++; }
         }
         if (path == 1 || path == 2) { push(0); leftMostPos = col; col--; row--; }
         else if (path == 3) { push(1); leftMostPos = col + 1; row--; }
         else if (path == 4) { push(2); col--; }
         else {
-            while (col >= 0 || row >= 0) { if (row >= 0) push(3); col--; row--; }
+            // off the left / top edge: the remaining rows are soft-clipped
+            if (row >= 0) {
+                const uint32_t cnt = (uint32_t)(row + 1);
+                if (curOp == 3u) curLen += cnt;
+                else { push(3); curLen = cnt; }
+            }
             break;
         }
     }
-    ops[nops >> 5] = acc;
-    // cigarStr = reverse(ops); strip leading / trailing S,I,D into S (diff-- per I/D)
-    auto opAt = [&](int i) -> uint32_t { int p = nops - 1 - i; return (uint32_t)(ops[p >> 5] >> ((p & 31) * 2)) & 3u; };  // i in cigarStr order
-    int left = 0, right = 0;
-    for (int i = 0; i < nops; ++i) {
-        uint32_t t = opAt(i);
-        if (t == 3) left++;
-        else if (t == 1 || t == 2) { left++; diff--; }
-        else break;
+    if (curLen) { if (nruns < GW_RUN_CAP) runs[nruns] = (curLen << 2) | curOp; ++nruns; }
+    bool overflow = nruns > GW_RUN_CAP;
+    const int nr = overflow ? GW_RUN_CAP : nruns;
+    // cigarStr = reverse(ops): its first run is runs[nr-1]. Leading / trailing S,I,D become S (diff-- per I/D base) (:599-636)
+    int left = 0, right = 0, L = 0, R = 0;
+    for (int i = nr - 1; i >= 0; --i) {
+        const uint32_t t = runs[i] & 3u, len = runs[i] >> 2;
+        if (t == 0u) break;
+        left += (int)len; ++L;
+        if (t != 3u) diff -= (int)len;
     }
-    for (int i = nops - 1; i >= left; --i) {
-        uint32_t t = opAt(i);
-        if (t == 3) right++;
-        else if (t == 1 || t == 2) { right++; diff--; }
-        else break;
+    for (int i = 0; i < nr - L; ++i) {
+        const uint32_t t = runs[i] & 3u, len = runs[i] >> 2;
+        if (t == 0u) break;
+        right += (int)len; ++R;
+        if (t != 3u) diff -= (int)len;
     }
-    // run-length encode: left x S, middle, right x S
     int n = 0;
-    uint32_t curOp = 0xFFFFFFFFu, curLen = 0;
-    bool overflow = false;
-    auto emit = [&](uint32_t bamOp, uint32_t len) {
-        if (len == 0) return;
-        if (bamOp == curOp) { curLen += len; return; }
-        if (curOp != 0xFFFFFFFFu) { if (n < GW_CIG_CAP) cig_out[n] = (curLen << 4) | curOp; else overflow = true; ++n; }
-        curOp = bamOp; curLen = len;
-    };
-    emit(GW_OP_S, (uint32_t)left);
-    for (int i = left; i < nops - right; ++i) {
-        uint32_t t = opAt(i);
-        emit(t == 0 ? GW_OP_M : t == 1 ? GW_OP_I : t == 2 ? GW_OP_D : GW_OP_S, 1);
+    if (left > 0) { cig_out[n] = ((uint32_t)left << 4) | GW_OP_S; ++n; }
+    for (int i = nr - 1 - L; i >= R; --i) {
+        const uint32_t t = runs[i] & 3u, len = runs[i] >> 2;
+        if (n < GW_CIG_CAP) cig_out[n] = (len << 4) | (t == 0u ? GW_OP_M : t == 1u ? GW_OP_I : t == 2u ? GW_OP_D : GW_OP_S);
+        else overflow = true;
+        ++n;
     }
-    emit(GW_OP_S, (uint32_t)right);
-    if (curOp != 0xFFFFFFFFu) { if (n < GW_CIG_CAP) cig_out[n] = (curLen << 4) | curOp; else overflow = true; ++n; }
+    if (right > 0) { if (n < GW_CIG_CAP) cig_out[n] = ((uint32_t)right << 4) | GW_OP_S; else overflow = true; ++n; }
     out->valid = 1; out->pos = leftMostPos; out->diff = diff; out->cig_n = n < GW_CIG_CAP ? n : GW_CIG_CAP; out->cig_overflow = overflow;
 }
 

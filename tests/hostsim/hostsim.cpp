@@ -113,13 +113,55 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
         const bool fused = !(getenv("GWSIM_ROUNDS") && atoi(getenv("GWSIM_ROUNDS")));
         GwFusedParams fp;
         fp.q_lf = getenv("GWSIM_Q_LF") ? atoi(getenv("GWSIM_Q_LF")) : 4;
+        fp.stick = 32;
         fp.q_cols = getenv("GWSIM_Q_COLS") ? atoi(getenv("GWSIM_Q_COLS")) : 8;
         auto rounds = [&](std::vector<uint32_t> cur) {
             if (fused) {   // like the fused kernel: every read is driven to completion by one lane, tick by tick
                 for (uint32_t slot : cur) {
                     GwSlab s(slabs[slot]);
+                    GwSearchLane L;
+                    L.base = L.c_off = -1; L.mid = 0;
                     int lp = gw_fused_start(env, s, slot);
-                    while (lp != GW_LP_FETCH) lp = gw_fused_tick(lp, env, s, slot, fp, hist.data(), 1);
+                    while (lp != GW_LP_FETCH) lp = gw_fused_tick(lp, env, s, slot, L, fp, hist.data(), 1);
+                }
+                return;
+            }
+            if (getenv("GWSIM_ROUNDS") && atoi(getenv("GWSIM_ROUNDS")) == 2) {   // like the pool kernel: S / L / D phases over a pool of reads
+                const uint32_t bud = step_budget ? step_budget : 32;
+                while (!cur.empty()) {
+                    std::vector<uint32_t> next, fr;
+                    for (uint32_t slot : cur) {
+                        GwSlab s(slabs[slot]);
+                        GwSearchLane L;
+                        L.base = L.c_off = -1; L.mid = 0;
+                        int r = gw_resume_read(env, s, slot, gw_no_queues());
+                        uint32_t budget = bud;
+                        while (r == GW_STEP_CONTINUE) {
+                            if (!L.mid) r = gw_search_poll(env, s, slot, gw_no_queues(), L);
+                            if (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try(env, s, L);
+                            if (r == GW_STEP_CONTINUE) {
+                                if (--budget == 0 && !L.mid) { next.push_back(slot); break; }
+                                else if (budget == 0) budget = 1;
+                            }
+                        }
+                        if (r == GW_STEP_PARKED) {
+                            next.push_back(slot);
+                            for (int f = 0; f < s.ctx()->pend_n; ++f) if (s.ctx()->pend[f].kind == 2) fr.push_back(slot * 2u + (uint32_t)f);
+                        }
+                    }
+                    for (uint32_t id : fr) {
+                        GwReadCtx* c = reinterpret_cast<GwReadCtx*>(slabs[id >> 1]);
+                        uint32_t steps = 0;
+                        c->pend[id & 1u].textpos = gw_sa_get(env.ix, c->pend[id & 1u].fm, c->pend[id & 1u].sa_index, &steps);
+                        c->occ_locate += steps;
+                    }
+                    for (uint32_t id : fr) {
+                        GwSlab s(slabs[id >> 1]);
+                        if (s.ctx()->phase == GW_PH_WAIT_EXACT) continue;
+                        GwJob job;
+                        gw_verify_frag(env, s, &job, (int)(id & 1u), hist.data(), 1);
+                    }
+                    cur.swap(next);
                 }
                 return;
             }

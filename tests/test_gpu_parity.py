@@ -192,7 +192,8 @@ def test_sam_parity_scalar_scan_and_small_slab(small):
     compare(small["idx"], small["oidx"], reads, gw.AlignmentConfig(k=3), dict(k=3), scan_coop=0, slab_words=1024, wave_reads=400)
 
 
-@pytest.mark.parametrize("opts", [dict(fused=0), dict(fused=0, tail_steps=3), dict(fused=1, q_lf=1, q_cols=1), dict(fused=1, q_lf=7, q_cols=33)])
+@pytest.mark.parametrize("opts", [dict(fused=0), dict(fused=0, tail_steps=3), dict(fused=1, q_lf=1, q_cols=1), dict(fused=1, q_lf=7, q_cols=33),
+                                  dict(fused=2, pool_budget=3, pool_tail=0), dict(fused=2, pool_tail=1024), dict(fused=2, pool_budget=1000, pool_blocks=1)])
 def test_sam_parity_round_mode_and_slice_sizes(small, opts):
     # the round-based kernels (search / locate / verify launched per round) and the fused lane program must agree with the oracle
     # whatever the slice sizes are
