@@ -1,2 +1,439 @@
-// placeholder main, replaced below
-int main() { return 0; }
+// gw_cli.cpp — `genome-weaver bwt <fasta>` and `genome-weaver align -r ref.fa reads.fastq > out.sam` over the C-ABI of
+// include/gw_align.h (libgwalign.so). Same sub-commands, flags and output as the reference's command line
+// (reference, align/src/main/java/org/utgenome/weaver/: GenomeWeaver.java:64-91, align/BWTransform.java:68-90,
+// align/Align.java:76-104,188-195, align/AlignmentConfig.java:40-72, align/AlignmentScoreConfig.java:37-77,
+// align/record/ReadReaderFactory.java:126-257, align/SAMOutput.java:51-82).
+//
+// The reference aligns one read per call on one thread; here the host is a pipeline
+//   reader (FASTQ/FASTA -> batches) -> one worker per GPU (gw_align_batch + gw_sam_format) -> writer (batch order)
+// with every GPU holding its own replica of the index (reads shard, nothing is exchanged between devices).
+// SAM lines come out in input order, exactly as the reference's sequential loop prints them.
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <chrono>
+#include <condition_variable>
+#include <deque>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/gw_align.h"
+
+namespace {
+
+struct Batch {
+    uint64_t seq = 0;           // position of the batch in the input
+    uint32_t n = 0;
+    std::string names, bases, quals;
+    std::vector<uint64_t> name_off{0}, base_off{0}, qual_off{0};
+    bool has_qual = true;       // FASTA reads and -q carry no quality (qual == null -> "*")
+    std::string sam;            // SAM text of the batch (filled by a worker)
+    int64_t abort_read = -1;    // first read on which the reference throws (its run stops there), -1: none
+    gw_counters_t counters{};
+    void add(const std::string& name, const std::string& seq_, const std::string* qual) {
+        names += name; name_off.push_back(names.size());
+        bases += seq_; base_off.push_back(bases.size());
+        if (qual) quals += *qual; else has_qual = false;
+        qual_off.push_back(quals.size());
+        ++n;
+    }
+};
+
+// ---- read files (ReadReaderFactory.createReader :126-153) ---------------------------------------------------------
+bool ends_with(const std::string& s, const char* suf) {
+    const size_t n = strlen(suf);
+    return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
+}
+
+class LineReader {   // 4 MB buffered line reader (the reference wraps its stream in a 4 MB BufferedReader, :141)
+  public:
+    explicit LineReader(FILE* f) : f_(f), buf_(4u << 20) {}
+    bool next(std::string& line) {
+        line.clear();
+        for (;;) {
+            if (pos_ == len_) {
+                len_ = fread(buf_.data(), 1, buf_.size(), f_);
+                pos_ = 0;
+                if (len_ == 0) return !line.empty() || pending_;
+            }
+            pending_ = true;
+            const char* p = buf_.data() + pos_;
+            const char* e = (const char*)memchr(p, '\n', len_ - pos_);
+            if (e) {
+                line.append(p, e - p);
+                pos_ += (size_t)(e - p) + 1;
+                pending_ = false;
+                if (!line.empty() && line.back() == '\r') line.pop_back();
+                return true;
+            }
+            line.append(p, len_ - pos_);
+            pos_ = len_;
+        }
+    }
+  private:
+    FILE* f_;
+    std::vector<char> buf_;
+    size_t pos_ = 0, len_ = 0;
+    bool pending_ = false;
+};
+
+std::string trim(const std::string& s) {
+    size_t a = 0, b = s.size();
+    while (a < b && (unsigned char)s[a] <= ' ') ++a;
+    while (b > a && (unsigned char)s[b - 1] <= ' ') --b;
+    return s.substr(a, b - a);
+}
+
+// FASTQ: 4 lines per record; read name = header line minus '@' (lens FASTQ.scala:35-52)
+struct FastqSource {
+    LineReader lr;
+    std::string l1, l2, l3, l4;
+    explicit FastqSource(FILE* f) : lr(f) {}
+    bool next(Batch& b) {
+        for (;;) {
+            if (!lr.next(l1)) return false;
+            if (!l1.empty()) break;
+        }
+        if (!lr.next(l2) || !lr.next(l3) || !lr.next(l4)) return false;   // truncated record: stop like FastqReader does at EOF
+        b.add(l1[0] == '@' ? l1.substr(1) : l1, trim(l2), &l4);
+        return true;
+    }
+};
+
+// FASTA reads: name = first whitespace-delimited token of the description line, sequence lines concatenated, no quality
+struct FastaSource {
+    LineReader lr;
+    std::string line, pending_name, seq;
+    bool have = false, eof = false;
+    explicit FastaSource(FILE* f) : lr(f) {}
+    static std::string pick_name(const std::string& desc) {
+        size_t a = 0;
+        while (a < desc.size() && (unsigned char)desc[a] <= ' ') ++a;
+        size_t b = a;
+        while (b < desc.size() && (unsigned char)desc[b] > ' ') ++b;
+        return desc.substr(a, b - a);
+    }
+    bool next(Batch& b) {
+        while (!eof) {
+            if (!lr.next(line)) { eof = true; break; }
+            if (!line.empty() && line[0] == '>') {
+                const std::string nm = pick_name(line.substr(1));
+                if (have) { b.add(pending_name, seq, nullptr); pending_name = nm; seq.clear(); return true; }
+                have = true; pending_name = nm; seq.clear();
+            } else if (have)
+                seq += trim(line);
+        }
+        if (have) { b.add(pending_name, seq, nullptr); have = false; return true; }
+        return false;
+    }
+};
+
+// ---- bounded queues between the pipeline stages ---------------------------------------------------------------------
+template <class T>
+class Channel {
+  public:
+    explicit Channel(size_t cap) : cap_(cap) {}
+    void push(T v) {
+        std::unique_lock<std::mutex> g(m_);
+        not_full_.wait(g, [&] { return q_.size() < cap_ || closed_; });
+        q_.push_back(std::move(v));
+        not_empty_.notify_one();
+    }
+    bool pop(T& v) {
+        std::unique_lock<std::mutex> g(m_);
+        not_empty_.wait(g, [&] { return !q_.empty() || closed_; });
+        if (q_.empty()) return false;
+        v = std::move(q_.front());
+        q_.pop_front();
+        not_full_.notify_one();
+        return true;
+    }
+    void close() {
+        std::lock_guard<std::mutex> g(m_);
+        closed_ = true;
+        not_empty_.notify_all();
+        not_full_.notify_all();
+    }
+  private:
+    std::mutex m_;
+    std::condition_variable not_full_, not_empty_;
+    std::deque<T> q_;
+    size_t cap_;
+    bool closed_ = false;
+};
+
+typedef std::unique_ptr<Batch> BatchPtr;
+
+struct Options {
+    std::string cmd, ref, query;
+    std::vector<std::string> files;
+    gw_config_t cfg;
+    bool silent = false, stats = false, keep_going = false;
+    int gpus = 1, device = 0;
+    uint32_t batch = 1u << 20;
+    std::vector<std::pair<std::string, long long>> tunables;
+};
+
+int usage() {
+    fprintf(stderr,
+            "usage: genome-weaver bwt <fasta> [--device D]\n"
+            "       genome-weaver align -r <ref.fa> [-q <query> | <reads.fastq|.fq|.fa|.fasta|.fan>] [-k K] [-s S] [-M n] [-N n] [-S n] [-P n] [-W n]\n"
+            "                           [-R besthit|allhits|topL] [-L n] [-m bsf] [--silent] [--gpus N] [--device D] [--batch reads] [--stats]\n"
+            "                           [--keep-going] [--opt name=value]\n");
+    return 1;
+}
+
+// one GPU: its own index replica and aligner; takes batches as they come, hands SAM text to the writer
+void worker(int device, const Options* o, Channel<BatchPtr>* in, Channel<BatchPtr>* out, std::string* err, double* busy_s) {
+    gw_index_t* ix = nullptr;
+    gw_aligner_t* al = nullptr;
+    auto fail = [&](const char* what) { *err = std::string(what) + ": " + gw_last_error(); };
+    if (gw_index_open(o->ref.c_str(), device, &ix) != GW_OK) fail("index");
+    else if (gw_aligner_create(ix, &o->cfg, &al) != GW_OK) fail("aligner");
+    if (err->empty()) for (auto& t : o->tunables) if (gw_aligner_set_option(al, t.first.c_str(), t.second) != GW_OK) { fail("option"); break; }
+    std::vector<gw_hit_t> hits;
+    std::vector<uint32_t> cig, lines;
+    BatchPtr b;
+    // a failed worker still drains its share so the pipeline ends
+    while (in->pop(b)) {
+        if (err->empty() && b->seq == 0 && b->n == 0) {   // start token: SAMOutput.init, "@SQ" lines from this worker's index
+            uint64_t n = 0;
+            gw_sam_header(ix, nullptr, &n);
+            b->sam.resize(n);
+            if (n && gw_sam_header(ix, &b->sam[0], &n) != GW_OK) fail("header");
+        }
+        if (err->empty() && b->n) {
+            const auto t0 = std::chrono::steady_clock::now();
+            hits.resize(std::max<size_t>(hits.size(), (size_t)b->n * 2 + 16));
+            cig.resize(std::max<size_t>(cig.size(), (size_t)b->n * 8 + 64));
+            uint64_t nh = 0, nc = 0;
+            int rc;
+            for (;;) {
+                nh = hits.size(); nc = cig.size();
+                rc = gw_align_batch(al, b->bases.data(), b->base_off.data(), b->n, hits.data(), &nh, cig.data(), &nc, &b->counters);
+                if (rc != GW_E_CAPACITY) break;
+                hits.resize(nh + 16); cig.resize(nc + 64);
+            }
+            if (rc != GW_OK) fail("align");
+            else {
+                for (uint64_t i = 0; i < nh; ++i)   // Align.java has no recovery: the first read the reference throws on ends its run
+                    if (hits[i].is_head && hits[i].status == GW_READ_REF_ABORT) { b->abort_read = hits[i].read_index; break; }
+                lines.assign(b->n, 0);
+                uint64_t len = b->bases.size() * 3 + b->names.size() * 2 + (size_t)b->n * 96 + 64;
+                for (;;) {
+                    b->sam.resize(len);
+                    rc = gw_sam_format(ix, b->names.data(), b->name_off.data(), b->bases.data(), b->base_off.data(),
+                                       b->has_qual ? b->quals.data() : nullptr, b->has_qual ? b->qual_off.data() : nullptr, b->n, hits.data(), nh,
+                                       cig.data(), &b->sam[0], &len, lines.data());
+                    if (rc != GW_E_CAPACITY) break;
+                    len += 64;
+                }
+                if (rc != GW_OK) fail("sam");
+                else {
+                    b->sam.resize(len);
+                    if (b->abort_read >= 0 && !o->keep_going) {   // keep the lines of the reads before the aborting one
+                        uint64_t keep = 0;
+                        for (int64_t r = 0; r < b->abort_read; ++r) keep += lines[(size_t)r];
+                        size_t p = 0;
+                        while (keep && p < b->sam.size()) { if (b->sam[p] == '\n') --keep; ++p; }
+                        b->sam.resize(p);
+                    }
+                }
+            }
+            *busy_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        }
+        out->push(std::move(b));
+    }
+    if (al) gw_aligner_destroy(al);
+    if (ix) gw_index_close(ix);
+}
+
+bool parse_ll(const char* s, long long* v) {
+    char* e = nullptr;
+    *v = strtoll(s, &e, 10);
+    return e && *e == 0 && e != s;
+}
+
+int cmd_bwt(int argc, char** argv) {
+    std::string fasta;
+    long long device = 0;
+    for (int i = 0; i < argc; ++i) {
+        if (!strcmp(argv[i], "--device") && i + 1 < argc) { if (!parse_ll(argv[++i], &device)) return usage(); }
+        else if (argv[i][0] == '-') return usage();
+        else fasta = argv[i];
+    }
+    if (fasta.empty()) return usage();
+    if (gw_index_build(fasta.c_str(), (int)device) != GW_OK) {
+        fprintf(stderr, "genome-weaver bwt: %s\n", gw_last_error());
+        return 1;
+    }
+    return 0;
+}
+
+int cmd_align(int argc, char** argv) {
+    Options o;
+    gw_config_default(&o.cfg);
+    for (int i = 0; i < argc; ++i) {
+        const std::string a = argv[i];
+        auto need = [&](long long* v) { return i + 1 < argc && parse_ll(argv[++i], v); };
+        long long v = 0;
+        if (a == "-r" && i + 1 < argc) o.ref = argv[++i];
+        else if (a == "-q" && i + 1 < argc) o.query = argv[++i];
+        else if (a == "-k" && i + 1 < argc) o.cfg.k = strtof(argv[++i], nullptr);
+        else if (a == "-s") { if (!need(&v)) return usage(); o.cfg.num_split_allowed = (int)v; }
+        else if (a == "-M") { if (!need(&v)) return usage(); o.cfg.match_score = (int)v; }
+        else if (a == "-N") { if (!need(&v)) return usage(); o.cfg.mismatch_penalty = (int)v; }
+        else if (a == "-S") { if (!need(&v)) return usage(); o.cfg.split_open_penalty = (int)v; }
+        else if (a == "-P") { if (!need(&v)) return usage(); o.cfg.indel_end_skip = (int)v; }
+        else if (a == "-W") { if (!need(&v)) return usage(); o.cfg.band_width = (int)v; }
+        else if (a == "-L") { if (!need(&v)) return usage(); o.cfg.top_l = (int)v; }
+        else if ((a == "-g" || a == "-e" || a == "-G" || a == "-E" || a == "--bssN") && i + 1 < argc) ++i;   // parsed by the reference, unused on the BSF path
+        else if (a == "--bss") {}
+        else if (a == "-R" && i + 1 < argc) {
+            std::string r = argv[++i];
+            for (char& c : r) c = (char)tolower((unsigned char)c);
+            if (r == "besthit") o.cfg.report_type = 0;
+            else if (r == "allhits") o.cfg.report_type = 1;
+            else if (r == "topl") o.cfg.report_type = 2;
+            else { fprintf(stderr, "unknown report type: %s\n", argv[i]); return 1; }
+        } else if (a == "-m" && i + 1 < argc) {
+            std::string m = argv[++i];
+            for (char& c : m) c = (char)tolower((unsigned char)c);
+            if (m != "bsf") { fprintf(stderr, "%s mode is not supported (this build accelerates -m bsf only)\n", argv[i]); return 1; }
+        } else if (a == "--silent") o.silent = true;
+        else if (a == "--stats") o.stats = true;
+        else if (a == "--keep-going") o.keep_going = true;
+        else if (a == "--gpus") { if (!need(&v) || v < 1) return usage(); o.gpus = (int)v; }
+        else if (a == "--device") { if (!need(&v)) return usage(); o.device = (int)v; }
+        else if (a == "--batch") { if (!need(&v) || v < 1) return usage(); o.batch = (uint32_t)v; }
+        else if (a == "--opt" && i + 1 < argc) {
+            const std::string kv = argv[++i];
+            const size_t eq = kv.find('=');
+            if (eq == std::string::npos || !parse_ll(kv.c_str() + eq + 1, &v)) return usage();
+            o.tunables.push_back({kv.substr(0, eq), v});
+        } else if (!a.empty() && a[0] == '-') return usage();
+        else o.files.push_back(a);
+    }
+    if (o.ref.empty()) { fprintf(stderr, "no reference (-r) is given\n"); return 1; }
+    if (o.query.empty() && o.files.empty()) { fprintf(stderr, "no query is given\n"); return 1; }   // Align.java:79-80
+
+    // open the read source before any device work (ReadReaderFactory.createReader: unsupported types fail up front)
+    FILE* f = nullptr;
+    bool fasta_reads = false;
+    if (o.query.empty()) {
+        const std::string& p = o.files[0];
+        if (ends_with(p, ".gz") || ends_with(p, ".snap")) { fprintf(stderr, "compressed read files are not supported: %s\n", p.c_str()); return 1; }
+        if (ends_with(p, ".fa") || ends_with(p, ".fasta") || ends_with(p, ".fan")) fasta_reads = true;
+        else if (!(ends_with(p, ".fastq") || ends_with(p, ".fq"))) { fprintf(stderr, "Unsupported file type: %s\n", p.c_str()); return 1; }
+        f = fopen(p.c_str(), "rb");
+        if (!f) { fprintf(stderr, "cannot open %s\n", p.c_str()); return 1; }
+    }
+
+    const auto t_start = std::chrono::steady_clock::now();
+    const int G = o.gpus;
+    Channel<BatchPtr> to_gpu((size_t)G * 2), done((size_t)G * 4);
+    std::vector<std::thread> workers;
+    std::vector<std::string> errs((size_t)G);
+    std::vector<double> busy((size_t)G, 0.0);
+    for (int g = 0; g < G; ++g)
+        workers.emplace_back(worker, o.device + g, &o, &to_gpu, &done, &errs[(size_t)g], &busy[(size_t)g]);
+
+    // writer: batches in input order; stops printing at the read the reference would have died on
+    uint64_t n_batches = 0, total_reads = 0;
+    gw_counters_t tot{};
+    bool aborted = false;
+    std::thread writer([&] {
+        std::map<uint64_t, BatchPtr> held;
+        uint64_t next = 0;
+        std::vector<char> obuf(8u << 20);
+        setvbuf(stdout, obuf.data(), _IOFBF, obuf.size());
+        BatchPtr b;
+        while (done.pop(b)) {
+            held[b->seq] = std::move(b);
+            for (auto it = held.find(next); it != held.end(); it = held.find(next)) {
+                Batch& cur = *it->second;
+                if (!aborted) {
+                    if (!o.silent) fwrite(cur.sam.data(), 1, cur.sam.size(), stdout);
+                    total_reads += cur.n;
+                    tot.fm_searches += cur.counters.fm_searches; tot.sw_calls += cur.counters.sw_calls;
+                    tot.cutoffs += cur.counters.cutoffs; tot.filtered += cur.counters.filtered;
+                    tot.occ_lookups_scan += cur.counters.occ_lookups_scan; tot.occ_lookups_search += cur.counters.occ_lookups_search;
+                    tot.occ_lookups_locate += cur.counters.occ_lookups_locate; tot.gpu_launches += cur.counters.gpu_launches;
+                    if (cur.abort_read >= 0 && !o.keep_going) {
+                        aborted = true;
+                        fprintf(stderr, "genome-weaver align: the reference aborts on read #%llu (%s); output ends there like the reference's (use --keep-going to skip such reads)\n",
+                                (unsigned long long)(total_reads - cur.n + (uint64_t)cur.abort_read),
+                                cur.names.substr(cur.name_off[(size_t)cur.abort_read], cur.name_off[(size_t)cur.abort_read + 1] - cur.name_off[(size_t)cur.abort_read]).c_str());
+                    }
+                }
+                held.erase(it);
+                ++next;
+            }
+        }
+        fflush(stdout);
+    });
+
+    // reader (this thread): batch 0 is the start token that carries the SAM header back
+    {
+        BatchPtr tok(new Batch());
+        tok->seq = n_batches++;
+        to_gpu.push(std::move(tok));
+    }
+    if (!o.query.empty()) {   // ReadReaderFactory.singleQueryReader :165-190: one read named "read", no quality
+        BatchPtr b(new Batch());
+        b->seq = n_batches++;
+        b->add("read", o.query, nullptr);
+        to_gpu.push(std::move(b));
+    } else {
+        FastqSource fq(f);
+        FastaSource fa(f);
+        for (;;) {
+            BatchPtr b(new Batch());
+            b->seq = n_batches;
+            b->bases.reserve((size_t)o.batch * 104);
+            while (b->n < o.batch && (fasta_reads ? fa.next(*b) : fq.next(*b))) {}
+            if (!b->n) break;
+            ++n_batches;
+            const bool last = b->n < o.batch;
+            to_gpu.push(std::move(b));
+            if (last) break;
+        }
+        fclose(f);
+    }
+    to_gpu.close();
+    for (auto& w : workers) w.join();
+    done.close();
+    writer.join();
+    int rc = 0;
+    for (int g = 0; g < G; ++g)
+        if (!errs[(size_t)g].empty()) { fprintf(stderr, "genome-weaver align (device %d): %s\n", o.device + g, errs[(size_t)g].c_str()); rc = 1; }
+    if (o.stats) {
+        const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
+        double b = 0;
+        for (double x : busy) b += x;
+        fprintf(stderr,
+                "{\"reads\": %llu, \"wall_s\": %.3f, \"reads_per_s\": %.0f, \"gpus\": %d, \"gpu_busy_s\": %.3f, \"fm_searches\": %llu, \"sw_calls\": %llu, "
+                "\"cutoffs\": %llu, \"filtered\": %llu, \"occ_lookups\": %llu, \"gpu_launches\": %llu, \"aborted\": %s}\n",
+                (unsigned long long)total_reads, wall, wall > 0 ? total_reads / wall : 0.0, G, b, (unsigned long long)tot.fm_searches,
+                (unsigned long long)tot.sw_calls, (unsigned long long)tot.cutoffs, (unsigned long long)tot.filtered,
+                (unsigned long long)(tot.occ_lookups_scan + tot.occ_lookups_search + tot.occ_lookups_locate), (unsigned long long)tot.gpu_launches,
+                aborted ? "true" : "false");
+    }
+    return rc;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+    if (argc < 2) return usage();
+    const std::string cmd = argv[1];
+    if (cmd == "bwt") return cmd_bwt(argc - 2, argv + 2);
+    if (cmd == "align") return cmd_align(argc - 2, argv + 2);
+    return usage();
+}

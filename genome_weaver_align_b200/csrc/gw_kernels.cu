@@ -197,6 +197,7 @@ __global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_fused_kernel(GwSearchEnv
 struct GwPoolParams {
     uint32_t budget;     // search slices per read and round
     uint32_t tail_thr;   // pool size below which the CTA hands over
+    uint32_t cap;        // reads a CTA keeps in flight (<= GW_POOL): small work lists are spread over all CTAs of the grid
 };
 
 __global__ void __launch_bounds__(GW_POOL_THREADS) gw_pool_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
@@ -216,8 +217,8 @@ __global__ void __launch_bounds__(GW_POOL_THREADS) gw_pool_kernel(GwSearchEnv en
         if (tid == 0) {
             head = 0; refill_n = 0;
             n_ready[cur ^ 1] = 0; n_frags = 0;
-            if (!drained && pool < GW_POOL) {
-                const uint32_t want = GW_POOL - pool;
+            if (!drained && pool < pp.cap) {
+                const uint32_t want = pp.cap - pool;
                 const uint32_t first = atomicAdd(work_counter, want);
                 uint32_t got = 0;
                 if (first < n_active) got = min(want, n_active - first);
@@ -483,10 +484,10 @@ void gwk_fused(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const
     gw_fused_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, fp, n_active_dev);
 }
 void gwk_pool(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-              uint32_t budget, uint32_t tail_thr, uint32_t blocks, uint32_t* leftover, uint32_t* leftover_count) {
+              uint32_t budget, uint32_t tail_thr, uint32_t cap, uint32_t blocks, uint32_t* leftover, uint32_t* leftover_count) {
     if (!n_active) return;
     GwPoolParams pp;
-    pp.budget = budget; pp.tail_thr = tail_thr;
+    pp.budget = budget; pp.tail_thr = tail_thr; pp.cap = cap < 1 ? 1 : (cap > GW_POOL ? GW_POOL : cap);
     gw_pool_kernel<<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
 }
 void gwk_locate(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
