@@ -191,7 +191,12 @@ __global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_fused_kernel(GwSearchEnv
 // synchronised with each other and refill their pool from the global work list as reads finish. When the work list is
 // drained and a pool has shrunk below `tail_thr` reads, the CTA hands its remaining reads to the leftover list (they are
 // finished by gw_fused_kernel, whose lanes are independent).
+#ifndef GW_POOL_THREADS
 #define GW_POOL_THREADS 256
+#endif
+#ifndef GW_POOL_MINB
+#define GW_POOL_MINB 1
+#endif
 #define GW_POOL 1024
 
 struct GwPoolParams {
@@ -200,7 +205,7 @@ struct GwPoolParams {
     uint32_t cap;        // reads a CTA keeps in flight (<= GW_POOL): small work lists are spread over all CTAs of the grid
 };
 
-__global__ void __launch_bounds__(GW_POOL_THREADS) gw_pool_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
+__global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
                                                                   uint32_t* work_counter, GwU64x2* hist, GwPoolParams pp, uint32_t* leftover,
                                                                   uint32_t* leftover_count) {
     __shared__ uint32_t ready[2][GW_POOL];       // reads to resume / continue, this round and the next
