@@ -202,9 +202,25 @@ __global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_fused_kernel(GwSearchEnv
 struct GwPoolParams {
     uint32_t budget;     // search slices per read and round
     uint32_t tail_thr;   // pool size below which the CTA hands over
+    uint32_t taper;      // slices shrink over the last taper x blockDim reads of a phase (0: off)
     uint32_t cap;        // reads a CTA keeps in flight (<= GW_POOL): small work lists are spread over all CTAs of the grid
 };
 
+#ifdef GW_POOL_PROF
+// phase accounting of the pool kernel (diagnostic builds only): thread-cycles spent working / waiting at the barrier, per phase
+__device__ unsigned long long gw_pool_prof[8];
+#define GW_PROF_T(v) const long long v = clock64()
+#define GW_PROF_ADD(i, d) prof[i] += (unsigned long long)(d)
+extern "C" int gw_debug_pool_prof(unsigned long long* out, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, gw_pool_prof, sizeof(gw_pool_prof));
+    if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(gw_pool_prof, z, sizeof(z)); }
+    return 0;
+}
+#else
+#define GW_PROF_T(v)
+#define GW_PROF_ADD(i, d)
+#endif
 __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
                                                                   uint32_t* work_counter, GwU64x2* hist, GwPoolParams pp, uint32_t* leftover,
                                                                   uint32_t* leftover_count) {
@@ -217,7 +233,11 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(
     const GwRoundQueues noq = gw_no_queues();
     if (tid == 0) { n_ready[0] = n_ready[1] = 0; n_frags = 0; pool = 0; drained = 0; cur = 0; }
     __syncthreads();
+#ifdef GW_POOL_PROF
+    unsigned long long prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#endif
     for (;;) {
+        GW_PROF_T(t_round);
         // ---- refill the pool from the global work list
         if (tid == 0) {
             head = 0; refill_n = 0;
@@ -244,6 +264,8 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(
             break;
         }
         __syncthreads();
+        GW_PROF_T(t_s0);
+        GW_PROF_ADD(6, t_s0 - t_round);
         // ---- phase S
         {
             bool have = false;
@@ -258,7 +280,10 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(
                     slot = ready[c_idx][i];
                     s = GwSlab(slabs[slot]);
                     L.mid = 0;
+                    // the last reads of the list get shorter slices, so that the lanes reach the barrier together (a read whose
+                    // slice ends simply continues in the next round)
                     budget = pp.budget;
+                    if (pp.taper) { const uint32_t rem = nr - i, span = pp.taper * blockDim.x; if (rem < span) budget = max(pp.budget * rem / span, 4u); }
                     const int r0 = gw_resume_read(env, s, slot, noq);
                     if (r0 == GW_STEP_DONE) { atomicSub(&pool, 1u); continue; }
                     if (r0 == GW_STEP_PARKED) {   // exact hit: needs its locate only
@@ -284,9 +309,12 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(
                 }
             }
         }
+        GW_PROF_T(t_s1);
         __syncthreads();
         if (tid == 0) head = 0;
         __syncthreads();
+        GW_PROF_T(t_l0);
+        GW_PROF_ADD(0, t_s1 - t_s0); GW_PROF_ADD(1, t_l0 - t_s1); GW_PROF_ADD(7, 1);
         const uint32_t nf = n_frags;
         // ---- phase L: lanes stay in the LF loop and take the next fragment when their walk ends
         {
@@ -314,7 +342,10 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(
                 }
             }
         }
+        GW_PROF_T(t_l1);
         __syncthreads();
+        GW_PROF_T(t_d0);
+        GW_PROF_ADD(2, t_l1 - t_l0); GW_PROF_ADD(3, t_d0 - t_l1);
         // ---- phase D
         for (uint32_t i = tid; i < nf; i += blockDim.x) {
             const uint32_t id = frags[i];
@@ -323,10 +354,16 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(
             GwJob job;
             gw_verify_frag(env, s, &job, (int)(id & 1u), my_hist, stride);
         }
+        GW_PROF_T(t_d1);
         __syncthreads();
         if (tid == 0) cur = n_idx;
         __syncthreads();
+        GW_PROF_T(t_e);
+        GW_PROF_ADD(4, t_d1 - t_d0); GW_PROF_ADD(5, t_e - t_d1);
     }
+#ifdef GW_POOL_PROF
+    for (int i = 0; i < 8; ++i) atomicAdd(&gw_pool_prof[i], prof[i]);
+#endif
 }
 
 __global__ void gw_locate_kernel(GwIndexView ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
@@ -489,9 +526,10 @@ void gwk_fused(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const
     gw_fused_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, fp, n_active_dev);
 }
 void gwk_pool(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-              uint32_t budget, uint32_t tail_thr, uint32_t cap, uint32_t blocks, uint32_t* leftover, uint32_t* leftover_count) {
+              uint32_t budget, uint32_t tail_thr, uint32_t cap, uint32_t taper, uint32_t blocks, uint32_t* leftover, uint32_t* leftover_count) {
     if (!n_active) return;
     GwPoolParams pp;
+    pp.taper = taper;
     pp.budget = budget; pp.tail_thr = tail_thr; pp.cap = cap < 1 ? 1 : (cap > GW_POOL ? GW_POOL : cap);
     gw_pool_kernel<<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
 }
