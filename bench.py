@@ -247,16 +247,32 @@ def run_ours(args):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+        # Kernel families of one step. Search, locate and verification run inside ONE kernel family (gw_pool_kernel + gw_fused_kernel
+        # for its stragglers), so their lookups are charged to the same CUDA-event time: 64 B per occurrence-table lookup
+        # (search: 2 per bidirectional step; locate: 1 per LF step) + 4 B per SA sample.
         fams = {
             "scan": (counters["occ_lookups_scan"] * 64.0, fam_ms[0]),
-            "search": (counters["occ_lookups_search"] * 64.0, fam_ms[1]),
-            "locate": (counters["occ_lookups_locate"] * 64.0 + counters["sw_calls"] * 4.0, fam_ms[2]),
+            "search+locate+verify": ((counters["occ_lookups_search"] + counters["occ_lookups_locate"]) * 64.0 + counters["sw_calls"] * 4.0,
+                                     fam_ms[1] + fam_ms[2] + fam_ms[3]),
         }
         roof_all = {k: {"bytes": b, "ms": float(t), "gbs": (b / (t * 1e-3) / 1e9 if t > 0 else None)} for k, (b, t) in fams.items()}
-        roof_all["verify"] = {"ms": float(fam_ms[3]), "sw_calls": counters["sw_calls"]}
+        roof_all["search+locate+verify"].update(occ_lookups_search=counters["occ_lookups_search"], occ_lookups_locate=counters["occ_lookups_locate"],
+                                                sw_calls=counters["sw_calls"], fm_searches=counters["fm_searches"])
         roof_all["emit"] = {"ms": float(fam_ms[4])}
         dom = max(fams, key=lambda k: fams[k][1])
         ach = roof_all[dom]["gbs"] or 0.0
+        # the random-access bound, measured in this job: independent 64 B gathers over the same occurrence table
+        gbs, gms = C.c_double(0), C.c_double(0)
+        gather = None
+        if lib.gw_gather_benchmark(idx._h, 1, 1 << 28, 3, C.byref(gbs), C.byref(gms)) == 0:
+            gather = float(gbs.value)
+        traffic = None
+        try:   # DRAM bytes per step of the dominant kernel family from the committed ncu --set full capture (profiles/)
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            if tj.get("reads") == n and tj.get("genome_bp") == args.genome_bp:
+                traffic = tj["dram_bytes_per_step"]
+        except Exception:  # noqa: BLE001
+            pass
         value = world * n * args.steps / dev_time
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -267,8 +283,12 @@ def run_ours(args):
                                (genome.size / 128 * 64 * 2 + genome.size / 8 + genome.size * 3 / 8) / 1e9),
                            parallelism="reads sharded over %d GPU(s), index replicated, no collective" % world, index_built_by=how,
                            index_build_s=round(t_build, 2)),
-            "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                         "peak_source": peak_src, "note": "algorithmic bytes = occ lookups x 64 B; the 100 Mbp index (0.2 GB of blocks) is only partly L2-resident",
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
+                         "peak_source": peak_src, "random_gather_gbs": gather, "frac_of_random_gather": (ach / gather if gather else None),
+                         "note": "algorithmic bytes = occurrence-table lookups x 64 B (+4 B per SA sample) over the CUDA-event time of the kernel family; "
+                                 "random_gather_gbs = independent 64 B gathers over the same table measured in this job (the bound a dependent FM "
+                                 "step can approach); traffic = DRAM bytes of the family per step from the ncu capture in profiles/ (work areas, "
+                                 "DP history and thread stacks, not the index, dominate it)",
                          "families": roof_all},
             "e2e": {"value": world * n * args.steps / e2e_time, "unit": UNIT, "h2d_bytes_per_step": int(n * m + (n + 1) * 8),
                     "d2h_bytes_per_step": int(e_nh * 44 + e_nc * 4), "ms_per_step": 1000.0 * e2e_time / args.steps},

@@ -57,6 +57,7 @@ SYMBOLS = {
     "gw_aligner_last_timing": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "gw_sam_format": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, C.c_uint32, _P, C.c_uint64, _P, _P, C.POINTER(C.c_uint64), _P]),
     "gw_sam_header": (C.c_int, [_P, _P, C.POINTER(C.c_uint64)]),
+    "gw_gather_benchmark": (C.c_int, [_P, C.c_int, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "gw_rank_acgtn": (C.c_int, [_P, C.c_int, _P, C.c_uint32, _P]),
     "gw_locate": (C.c_int, [_P, C.c_int, _P, C.c_uint32, _P]),
     "gw_quick_scan": (C.c_int, [_P, _P, _P, C.c_uint32, C.c_int, _P]),

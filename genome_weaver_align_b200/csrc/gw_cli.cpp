@@ -13,6 +13,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <chrono>
 #include <condition_variable>
 #include <deque>
@@ -51,36 +52,48 @@ bool ends_with(const std::string& s, const char* suf) {
     return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
 }
 
-class LineReader {   // 4 MB buffered line reader (the reference wraps its stream in a 4 MB BufferedReader, :141)
+class LineReader {   // buffered line reader over a 16 MB window; lines are handed out as views into the window
   public:
-    explicit LineReader(FILE* f) : f_(f), buf_(4u << 20) {}
-    bool next(std::string& line) {
-        line.clear();
+    explicit LineReader(FILE* f) : f_(f), buf_(16u << 20) {}
+    // next line without its terminator; the view is valid until the next call
+    bool next(const char*& p, size_t& n) {
         for (;;) {
-            if (pos_ == len_) {
-                len_ = fread(buf_.data(), 1, buf_.size(), f_);
-                pos_ = 0;
-                if (len_ == 0) return !line.empty() || pending_;
-            }
-            pending_ = true;
-            const char* p = buf_.data() + pos_;
-            const char* e = (const char*)memchr(p, '\n', len_ - pos_);
+            const char* s = buf_.data() + pos_;
+            const char* e = (const char*)memchr(s, '\n', len_ - pos_);
             if (e) {
-                line.append(p, e - p);
-                pos_ += (size_t)(e - p) + 1;
-                pending_ = false;
-                if (!line.empty() && line.back() == '\r') line.pop_back();
+                p = s; n = (size_t)(e - s);
+                pos_ += n + 1;
+                if (n && p[n - 1] == '\r') --n;
                 return true;
             }
-            line.append(p, len_ - pos_);
-            pos_ = len_;
+            if (eof_) {
+                if (pos_ == len_) return false;
+                p = s; n = len_ - pos_;
+                pos_ = len_;
+                if (n && p[n - 1] == '\r') --n;
+                return true;
+            }
+            // refill: keep the unfinished line at the front of the window (grow it for lines longer than the window)
+            const size_t rest = len_ - pos_;
+            if (rest) memmove(buf_.data(), buf_.data() + pos_, rest);
+            if (rest == buf_.size()) buf_.resize(buf_.size() * 2);
+            pos_ = 0; len_ = rest;
+            const size_t got = fread(buf_.data() + len_, 1, buf_.size() - len_, f_);
+            len_ += got;
+            if (got == 0) eof_ = true;
         }
+    }
+    bool next(std::string& line) {
+        const char* p; size_t n;
+        if (!next(p, n)) { line.clear(); return false; }
+        line.assign(p, n);
+        return true;
     }
   private:
     FILE* f_;
     std::vector<char> buf_;
     size_t pos_ = 0, len_ = 0;
-    bool pending_ = false;
+    bool eof_ = false;
 };
 
 std::string trim(const std::string& s) {
@@ -90,18 +103,31 @@ std::string trim(const std::string& s) {
     return s.substr(a, b - a);
 }
 
-// FASTQ: 4 lines per record; read name = header line minus '@' (lens FASTQ.scala:35-52)
+// FASTQ: 4 lines per record; read name = header line minus '@' (lens FASTQ.scala:35-52). Lines go straight from the
+// reader's window into the batch arrays.
 struct FastqSource {
     LineReader lr;
-    std::string l1, l2, l3, l4;
     explicit FastqSource(FILE* f) : lr(f) {}
     bool next(Batch& b) {
+        const char* p; size_t n;
         for (;;) {
-            if (!lr.next(l1)) return false;
-            if (!l1.empty()) break;
+            if (!lr.next(p, n)) return false;
+            if (n) break;
         }
-        if (!lr.next(l2) || !lr.next(l3) || !lr.next(l4)) return false;   // truncated record: stop like FastqReader does at EOF
-        b.add(l1[0] == '@' ? l1.substr(1) : l1, trim(l2), &l4);
+        const size_t n0 = b.names.size(), b0 = b.bases.size();
+        if (p[0] == '@') { ++p; --n; }
+        b.names.append(p, n);
+        bool ok = lr.next(p, n);
+        if (ok) {
+            while (n && (unsigned char)p[0] <= ' ') { ++p; --n; }
+            while (n && (unsigned char)p[n - 1] <= ' ') --n;
+            b.bases.append(p, n);
+            ok = lr.next(p, n) && lr.next(p, n);
+        }
+        if (!ok) { b.names.resize(n0); b.bases.resize(b0); return false; }   // truncated record: stop like FastqReader does at EOF
+        b.quals.append(p, n);
+        b.name_off.push_back(b.names.size()); b.base_off.push_back(b.bases.size()); b.qual_off.push_back(b.quals.size());
+        ++b.n;
         return true;
     }
 };
@@ -190,13 +216,15 @@ int usage() {
 }
 
 // one GPU: its own index replica and aligner; takes batches as they come, hands SAM text to the writer
-void worker(int device, const Options* o, Channel<BatchPtr>* in, Channel<BatchPtr>* out, std::string* err, double* busy_s) {
+void worker(int device, const Options* o, Channel<BatchPtr>* in, Channel<BatchPtr>* out, std::string* err, double* busy_s, double* open_s) {
+    const auto t_open = std::chrono::steady_clock::now();
     gw_index_t* ix = nullptr;
     gw_aligner_t* al = nullptr;
     auto fail = [&](const char* what) { *err = std::string(what) + ": " + gw_last_error(); };
     if (gw_index_open(o->ref.c_str(), device, &ix) != GW_OK) fail("index");
     else if (gw_aligner_create(ix, &o->cfg, &al) != GW_OK) fail("aligner");
     if (err->empty()) for (auto& t : o->tunables) if (gw_aligner_set_option(al, t.first.c_str(), t.second) != GW_OK) { fail("option"); break; }
+    *open_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_open).count();
     std::vector<gw_hit_t> hits;
     std::vector<uint32_t> cig, lines;
     BatchPtr b;
@@ -340,9 +368,9 @@ int cmd_align(int argc, char** argv) {
     Channel<BatchPtr> to_gpu((size_t)G * 2), done((size_t)G * 4);
     std::vector<std::thread> workers;
     std::vector<std::string> errs((size_t)G);
-    std::vector<double> busy((size_t)G, 0.0);
+    std::vector<double> busy((size_t)G, 0.0), opened((size_t)G, 0.0);
     for (int g = 0; g < G; ++g)
-        workers.emplace_back(worker, o.device + g, &o, &to_gpu, &done, &errs[(size_t)g], &busy[(size_t)g]);
+        workers.emplace_back(worker, o.device + g, &o, &to_gpu, &done, &errs[(size_t)g], &busy[(size_t)g], &opened[(size_t)g]);
 
     // writer: batches in input order; stops printing at the read the reference would have died on
     uint64_t n_batches = 0, total_reads = 0;
@@ -415,12 +443,13 @@ int cmd_align(int argc, char** argv) {
         if (!errs[(size_t)g].empty()) { fprintf(stderr, "genome-weaver align (device %d): %s\n", o.device + g, errs[(size_t)g].c_str()); rc = 1; }
     if (o.stats) {
         const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
-        double b = 0;
+        double b = 0, op = 0;
         for (double x : busy) b += x;
+        for (double x : opened) op = std::max(op, x);
         fprintf(stderr,
-                "{\"reads\": %llu, \"wall_s\": %.3f, \"reads_per_s\": %.0f, \"gpus\": %d, \"gpu_busy_s\": %.3f, \"fm_searches\": %llu, \"sw_calls\": %llu, "
+                "{\"reads\": %llu, \"wall_s\": %.3f, \"reads_per_s\": %.0f, \"index_open_s\": %.3f, \"reads_per_s_after_open\": %.0f, \"gpus\": %d, \"worker_busy_s\": %.3f, \"fm_searches\": %llu, \"sw_calls\": %llu, "
                 "\"cutoffs\": %llu, \"filtered\": %llu, \"occ_lookups\": %llu, \"gpu_launches\": %llu, \"aborted\": %s}\n",
-                (unsigned long long)total_reads, wall, wall > 0 ? total_reads / wall : 0.0, G, b, (unsigned long long)tot.fm_searches,
+                (unsigned long long)total_reads, wall, wall > 0 ? total_reads / wall : 0.0, op, wall > op ? total_reads / (wall - op) : 0.0, G, b, (unsigned long long)tot.fm_searches,
                 (unsigned long long)tot.sw_calls, (unsigned long long)tot.cutoffs, (unsigned long long)tot.filtered,
                 (unsigned long long)(tot.occ_lookups_scan + tot.occ_lookups_search + tot.occ_lookups_locate), (unsigned long long)tot.gpu_launches,
                 aborted ? "true" : "false");

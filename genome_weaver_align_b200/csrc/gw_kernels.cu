@@ -553,6 +553,32 @@ void gwk_emit_write(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevC
                     const unsigned long long* cig_off, void* recs, unsigned long long rec_cap, uint32_t* cigs, unsigned long long cig_cap) {
     if (n) gw_emit_write_kernel<<<gw_grid(n, 128), 128, 0, st>>>(slabs, n, cfg, read_base, rec_off, cig_off, (GwHitRec*)recs, rec_cap, cigs, cig_cap);
 }
+// Measurement aid (SURVEY.md 8d "random-access roofline"): every thread does `per_thread` INDEPENDENT rank queries at pseudo-random
+// BWT positions (one 64 B occurrence block each, four 128-bit loads, all issued before the first use). This is the rate the memory
+// system delivers for the access pattern of an FM step when nothing serialises the lookups; the search kernels, whose lookups
+// depend on each other through the automaton, are reported against it as well as against the streaming peak.
+__global__ void __launch_bounds__(256) gw_gather_bench_kernel(GwIndexView ix, int which, uint32_t per_thread, uint32_t seed, uint32_t* sink) {
+    const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t nblk = (uint32_t)((ix.N + 127) >> 7);
+    uint32_t x = (gtid + 1u) * 2654435761u ^ seed, acc = 0;
+    for (uint32_t j = 0; j < per_thread; j += 4) {
+        GwBlk b[4];
+        uint32_t r[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            x ^= x << 13; x ^= x >> 17; x ^= x << 5;   // xorshift32
+            const uint32_t blk = (uint32_t)(((u64)x * nblk) >> 32);
+            r[u] = x & 127u;
+            b[u] = gw_load_block(ix.occ[which] + blk);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { uint32_t o[4]; gw_rank4(b[u], r[u], o); acc += o[0] ^ o[1] ^ o[2] ^ o[3]; }
+    }
+    if (acc == 0x9E3779B9u) sink[0] = acc;   // keeps the loads alive
+}
+void gwk_gather_bench(cudaStream_t st, const GwIndexView& ix, int which, uint32_t blocks, uint32_t per_thread, uint32_t seed, uint32_t* sink) {
+    gw_gather_bench_kernel<<<blocks, 256, 0, st>>>(ix, which, per_thread, seed, sink);
+}
 void gwk_rank_acgtn(cudaStream_t st, const GwIndexView& ix, int which, const uint32_t* pos, uint32_t n, uint32_t* out) {
     if (n) gw_rank_acgtn_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, which, pos, n, out);
 }

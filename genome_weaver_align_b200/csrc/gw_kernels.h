@@ -21,6 +21,7 @@ void gwk_scan2(cudaStream_t st, const uint32_t* a, const uint32_t* b, uint32_t n
                unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot);
 void gwk_emit_write(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t read_base, const unsigned long long* rec_off,
                     const unsigned long long* cig_off, void* recs, unsigned long long rec_cap, uint32_t* cigs, unsigned long long cig_cap);
+void gwk_gather_bench(cudaStream_t st, const GwIndexView& ix, int which, uint32_t blocks, uint32_t per_thread, uint32_t seed, uint32_t* sink);
 void gwk_rank_acgtn(cudaStream_t st, const GwIndexView& ix, int which, const uint32_t* pos, uint32_t n, uint32_t* out);
 void gwk_locate_rows(cudaStream_t st, const GwIndexView& ix, int which, const uint32_t* rows, uint32_t n, uint32_t* out);
 void gwk_scan_export(cudaStream_t st, u64* const* slabs, uint32_t n, int strand, uint32_t* out);

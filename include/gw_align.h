@@ -142,6 +142,9 @@ int gw_sam_header(const gw_index_t*, char* out, uint64_t* out_len);
 /* ---- component entry points (used by the parity tests; each replaces one reference method) ---- */
 /* FMIndexOnOccTable.rankACGTN (align/FMIndexOnOccTable.java:53-55) for n positions; which: 0 forward BWT, 1 reverse BWT; out n x 5 */
 int gw_rank_acgtn(const gw_index_t*, int which, const uint32_t* pos, uint32_t n, uint32_t* out);
+/* measurement aid, no reference counterpart: rate of INDEPENDENT random 64 B occurrence-block gathers (rank queries at
+ * random BWT positions of index `which`), the bound a dependent FM step can approach; about n_lookups gathers per iteration */
+int gw_gather_benchmark(const gw_index_t*, int which, uint64_t n_lookups, int iters, double* gb_per_s, double* ms_per_iter);
 /* SparseSuffixArray.get (align/SparseSuffixArray.java:141-161) for n SA rows */
 int gw_locate(const gw_index_t*, int which, const uint32_t* sa_rows, uint32_t n, uint32_t* out);
 /* FMQuickScan.scanMismatchLocations (align/strategy/FMQuickScan.java:66-94) for a read batch and strand (0 '+': scans the read,
