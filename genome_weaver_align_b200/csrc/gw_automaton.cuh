@@ -197,6 +197,26 @@ struct GwSearchLane {
     int32_t mid;     // 1: candidates of the current step remain
 };
 
+// the chain headed by `base` is complete: classify its fragments (park for locate + verification) or report it at once (:366-379)
+GW_COLD int gw_search_report(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq, int32_t base) {
+    GwReadCtx* c = s.ctx();
+    if (gw_begin_report(env, s, slot, base, rq)) {
+        c->phase = GW_PH_WAIT_VERIFY;
+        if (rq.counters) rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
+        return GW_STEP_PARKED;
+    }
+    gw_finish_report(env, s);
+    return c->phase == GW_PH_DONE ? GW_STEP_DONE : GW_STEP_CONTINUE;
+}
+
+// L.mid after a slice: 0 step finished, GW_MID_TRY candidates remain; with DEFER (warp-pool kernel) the rarely taken, long
+// continuations are not run inside the slice but left as GW_MID_SPLIT / GW_MID_REPORT for the caller, which runs them for
+// several lanes of the warp at once (gw_search_split, gw_search_report)
+#define GW_MID_TRY 1
+#define GW_MID_SPLIT 2
+#define GW_MID_REPORT 3
+
+template <bool DEFER = false>
 GW_HD int gw_search_poll(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq, GwSearchLane& L) {
     GwReadCtx* c = s.ctx();
     const int m = c->m;
@@ -209,13 +229,8 @@ GW_HD int gw_search_poll(const GwSearchEnv& env, const GwSlab& s, uint32_t slot,
     for (;;) {   // first fragment of the chain that still has bases to process (:366-379)
         if (!(gw_has_hit(C) || gw_is_clipped(C) || gw_remaining(C) == 0)) break;
         if (C->next_split < 0) {
-            if (gw_begin_report(env, s, slot, base, rq)) {
-                c->phase = GW_PH_WAIT_VERIFY;
-                if (rq.counters) rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
-                return GW_STEP_PARKED;
-            }
-            gw_finish_report(env, s);
-            return c->phase == GW_PH_DONE ? GW_STEP_DONE : GW_STEP_CONTINUE;
+            if (DEFER) { L.base = base; L.mid = GW_MID_REPORT; return GW_STEP_CONTINUE; }
+            return gw_search_report(env, s, slot, rq, base);
         }
         c_off = C->next_split;
         C = gw_st(s, c_off);
@@ -258,6 +273,7 @@ GW_COLD int gw_search_split(const GwSearchEnv& env, const GwSlab& s, const GwSea
     return GW_STEP_CONTINUE;
 }
 
+template <bool DEFER = false, int MAXH = GW_MAX_ROWS>
 GW_HD int gw_search_try(const GwSearchEnv& env, const GwSlab& s, GwSearchLane& L) {
     GwReadCtx* c = s.ctx();
     const GwDevConfig& cfg = env.cfg;
@@ -284,23 +300,33 @@ GW_HD int gw_search_try(const GwSearchEnv& env, const GwSlab& s, GwSearchLane& L
     if (ch < 0) {   // candidates exhausted without extending with the read's own base
         flags |= 1 << 4;
         Cp->state = flags;
+        if (DEFER) { L.mid = GW_MID_SPLIT; return GW_STEP_CONTINUE; }
         L.mid = 0;
         return gw_search_split(env, s, L);
     }
     int kk;
     const u64* tbl = gw_staircase_for(env, c, &kk);
-    u64 prev[GW_MAX_ROWS];
+    u64 prev[MAXH];
     {
         const u64* rows = gw_rows(Cp);
-        for (int i = 0; i < C.height; ++i) prev[i] = rows[i];
+        if constexpr (MAXH <= 8) {
+#pragma unroll
+            for (int i = 0; i < MAXH; ++i) prev[i] = i < C.height ? rows[i] : 0ULL;
+        } else {
+            for (int i = 0; i < C.height; ++i) prev[i] = rows[i];
+        }
     }
     GwSiSet nsi;
     gw_next_si(env.ix, &C, ch, &nsi, &c->occ_search);
     c->n_fm++;
-    const int32_t ns = gw_next_state(s, C, prev, ch, nsi, tbl, kk);
+    GwState built;
+    const int32_t ns = gw_next_state<MAXH>(s, C, prev, ch, nsi, tbl, kk, &built);
     if (ns == -2) { Cp->state = flags; gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
     if (ns >= 0) {
-        if (!gw_queue_add(s, cfg, gw_update(s, L.base, L.c_off, ns))) { Cp->state = flags; gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+        // the usual case — a chain of one state — takes its queue key from the register copy of the state just built
+        const bool ok = (L.c_off == L.base && built.next_split < 0) ? gw_queue_add_key(s, ns, gw_state_key_single(cfg, &built))
+                                                                    : gw_queue_add(s, cfg, gw_update(s, L.base, L.c_off, ns));
+        if (!ok) { Cp->state = flags; gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
         if (own) { Cp->state = flags; L.mid = 0; return GW_STEP_CONTINUE; }   // extended: the parent is dropped (:426-429)
     } else
         c->n_filt++;

@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_fused_kernel(GwSearchEnv
 #define GW_POOL_THREADS 256
 #endif
 #ifndef GW_POOL_MINB
-#define GW_POOL_MINB 1
+#define GW_POOL_MINB 2
 #endif
 #define GW_POOL 1024
 
@@ -204,6 +204,9 @@ struct GwPoolParams {
     uint32_t tail_thr;   // pool size below which the CTA hands over
     uint32_t taper;      // slices shrink over the last taper x blockDim reads of a phase (0: off)
     uint32_t cap;        // reads a CTA keeps in flight (<= GW_POOL): small work lists are spread over all CTAs of the grid
+    uint32_t batch;      // warp pools: lanes that must wait for a deferred continuation before the warp runs it
+    uint32_t age;        // warp pools: ... or this many trips since the first lane started waiting
+    uint32_t flush;      // flow kernel: once the work list is drained, a partial verification batch runs when this many lanes idle
 };
 
 #ifdef GW_POOL_PROF
@@ -221,6 +224,7 @@ extern "C" int gw_debug_pool_prof(unsigned long long* out, int reset) {
 #define GW_PROF_T(v)
 #define GW_PROF_ADD(i, d)
 #endif
+template <int MAXH>
 __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
                                                                   uint32_t* work_counter, GwU64x2* hist, GwPoolParams pp, uint32_t* leftover,
                                                                   uint32_t* leftover_count) {
@@ -295,7 +299,7 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(
                 }
                 int r = GW_STEP_CONTINUE;
                 if (!L.mid) r = gw_search_poll(env, s, slot, noq, L);
-                if (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try(env, s, L);
+                if (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try<false, MAXH>(env, s, L);
                 if (r == GW_STEP_CONTINUE) {
                     if (--budget == 0 && !L.mid) { ready[n_idx][atomicAdd(&n_ready[n_idx], 1u)] = slot; have = false; }
                     else if (budget == 0) budget = 1;   // finish the step that is under way
@@ -364,6 +368,149 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(
 #ifdef GW_POOL_PROF
     for (int i = 0; i < 8; ++i) atomicAdd(&gw_pool_prof[i], prof[i]);
 #endif
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Flow kernel: warp-level pools without rounds. Every warp owns two small FIFOs in shared memory — reads ready to (re)start
+// searching and fragments waiting for locate + verification — and loops over three kinds of warp-wide work:
+//   * search slices: one poll + one candidate extension per lane and trip; the long, rarely taken continuations (taking a read up /
+//     consuming verification results, split + soft-clip children, chain reporting) are deferred until `batch` lanes wait for one
+//     (or `age` trips passed, or nothing else can run), so that they run for several lanes at once instead of one lane while 31 wait,
+//   * pick-up: idle lanes take reads from the ready FIFO (refilled from the global work list, `cap` reads at a time),
+//   * a verification batch as soon as 32 fragments wait: every lane walks one fragment to its SA sample and runs its DP + traceback;
+//     the reads whose fragments are all done go back to the ready FIFO.
+// There is no per-round tail: a lane that parks or finishes a read takes the next one at once, and locate / DP always run with
+// (nearly) full warps.
+#define GW_RING 256
+#define GW_WARPS (GW_POOL_THREADS / 32)
+template <int MAXH>
+__global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
+                                                                  uint32_t* work_counter, GwU64x2* hist, GwPoolParams pp) {
+    __shared__ uint32_t ready_s[GW_WARPS][GW_RING];
+    __shared__ uint32_t frags_s[GW_WARPS][GW_RING];
+    const uint32_t FULL = 0xFFFFFFFFu, MASK = GW_RING - 1u;
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t* ready = ready_s[wid];
+    uint32_t* frags = frags_s[wid];
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const GwRoundQueues noq = gw_no_queues();
+    uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_pick = 0, age_cold = 0;
+    bool drained = false;
+    bool have = false;
+    GwSlab s;
+    GwSearchLane L;
+    L.base = L.c_off = -1; L.mid = 0;
+    uint32_t slot = 0;
+    for (;;) {
+        const uint32_t busy = __ballot_sync(FULL, have);
+        const uint32_t idle = ~busy;
+        const uint32_t n_ready = r_tail - r_head, n_fr = f_tail - f_head;
+        // ---- verification batch
+        if (n_fr >= 32u || (n_fr != 0u && n_ready == 0u && drained && (busy == 0u || (uint32_t)__popc(idle) >= pp.flush))) {
+            uint32_t nb = n_fr < 32u ? n_fr : 32u;
+            if (n_fr > 32u && (frags[(f_head + 31u) & MASK] >> 1) == (frags[(f_head + 32u) & MASK] >> 1)) nb = 31u;   // both fragments of a read in one batch
+            const uint32_t id = lane < nb ? frags[(f_head + lane) & MASK] : 0xFFFFFFFFu;
+            f_head += nb;
+            GwReadCtx* c = nullptr;
+            if (lane < nb) {   // locate
+                c = reinterpret_cast<GwReadCtx*>(slabs[id >> 1]);
+                GwPendFrag* pf = &c->pend[id & 1u];
+                uint32_t cursor = pf->sa_index;
+                const int fm = pf->fm;
+                int j = 0;
+                while ((cursor % GW_SSA_L) != 0) { cursor = gw_suffix_link(env.ix, fm, cursor); ++j; }
+                const uint32_t smp = gw_ld32(env.ix.ssa[fm] + cursor / GW_SSA_L);
+                pf->textpos = j == 0 ? smp : (uint32_t)(((u64)smp + (u64)j + env.ix.N) % env.ix.N);
+                atomicAdd(&c->occ_locate, (uint32_t)j);   // the two fragments of a read are walked by different lanes
+            }
+            __syncwarp();
+            if (lane < nb && c->phase != GW_PH_WAIT_EXACT) {   // exact hit: no verification (:490-494)
+                GwSlab sv(slabs[id >> 1]);
+                GwJob job;
+                gw_verify_frag(env, sv, &job, (int)(id & 1u), my_hist, stride);
+            }
+            __syncwarp();
+            const uint32_t nid = __shfl_down_sync(FULL, id, 1);
+            const bool last = lane < nb && (lane == nb - 1u || (nid >> 1) != (id >> 1));
+            const uint32_t bl = __ballot_sync(FULL, last);
+            if (last) ready[(r_tail + (uint32_t)__popc(bl & lt)) & MASK] = id >> 1;
+            r_tail += (uint32_t)__popc(bl);
+            __syncwarp();
+            continue;
+        }
+        // ---- pick-up (idle lanes take reads from the ready FIFO; refill from the global work list)
+        if (idle != 0u && (n_ready != 0u || !drained)) {
+            if ((uint32_t)__popc(idle) >= pp.batch || busy == 0u || ++age_pick >= pp.age) {
+                age_pick = 0;
+                uint32_t nrd = n_ready;
+                if (nrd < (uint32_t)__popc(idle) && !drained) {
+                    uint32_t first = 0;
+                    if (lane == 0) first = atomicAdd(work_counter, pp.cap);
+                    first = __shfl_sync(FULL, first, 0);
+                    uint32_t got = 0;
+                    if (first < n_active) got = min(pp.cap, n_active - first);
+                    if (first + pp.cap >= n_active) drained = true;
+                    if (lane < got) ready[(r_tail + lane) & MASK] = active ? active[first + lane] : first + lane;
+                    r_tail += got; nrd += got;
+                    __syncwarp();
+                }
+                int r0 = -1;
+                if (!have) {
+                    const uint32_t i = (uint32_t)__popc(idle & lt);
+                    if (i < nrd) {
+                        slot = ready[(r_head + i) & MASK];
+                        s = GwSlab(slabs[slot]);
+                        L.mid = 0;
+                        r0 = gw_resume_read(env, s, slot, noq);
+                        have = r0 == GW_STEP_CONTINUE;
+                    }
+                }
+                r_head += min((uint32_t)__popc(idle), nrd);
+                const uint32_t pk = __ballot_sync(FULL, r0 == GW_STEP_PARKED);   // exact hit: needs its locate only
+                if (r0 == GW_STEP_PARKED) frags[(f_tail + (uint32_t)__popc(pk & lt)) & MASK] = slot * 2u;
+                f_tail += (uint32_t)__popc(pk);
+                __syncwarp();
+                continue;
+            }
+        } else if (busy == 0u) {
+            if (n_fr == 0u && n_ready == 0u && drained) break;
+        }
+        // ---- one search slice per lane
+        int r = GW_STEP_CONTINUE;
+        if (have && L.mid == 0) r = gw_search_poll<true>(env, s, slot, noq, L);
+        if (have && r == GW_STEP_CONTINUE && L.mid == GW_MID_TRY) r = gw_search_try<true, MAXH>(env, s, L);
+        // ---- deferred continuations
+        {
+            const bool wants = have && r == GW_STEP_CONTINUE && L.mid >= GW_MID_SPLIT;
+            const uint32_t cold = __ballot_sync(FULL, wants);
+            if (cold != 0u) {
+                const uint32_t hot = __ballot_sync(FULL, have && r == GW_STEP_CONTINUE && L.mid < GW_MID_SPLIT);
+                if ((uint32_t)__popc(cold) >= pp.batch || hot == 0u || ++age_cold >= pp.age) {
+                    age_cold = 0;
+                    if (wants && L.mid == GW_MID_SPLIT) { L.mid = 0; r = gw_search_split(env, s, L); }
+                    if (wants && L.mid == GW_MID_REPORT) { L.mid = 0; r = gw_search_report(env, s, slot, noq, L.base); }
+                }
+            }
+        }
+        // ---- parked reads queue their fragments (both fragments of a read next to each other); finished reads just leave
+        bool f0 = false, f1 = false;
+        if (have && r == GW_STEP_PARKED) {
+            const GwReadCtx* c = s.ctx();
+            f0 = c->pend_n > 0 && c->pend[0].kind == 2;
+            f1 = c->pend_n > 1 && c->pend[1].kind == 2;
+        }
+        const uint32_t b_f0 = __ballot_sync(FULL, f0), b_f1 = __ballot_sync(FULL, f1);
+        if (b_f0 | b_f1) {
+            const uint32_t o = f_tail + (uint32_t)__popc(b_f0 & lt) + (uint32_t)__popc(b_f1 & lt);
+            if (f0) frags[o & MASK] = slot * 2u;
+            if (f1) frags[(o + (f0 ? 1u : 0u)) & MASK] = slot * 2u + 1u;
+            f_tail += (uint32_t)__popc(b_f0) + (uint32_t)__popc(b_f1);
+            __syncwarp();
+        }
+        if (have && r != GW_STEP_CONTINUE) have = false;
+    }
 }
 
 __global__ void gw_locate_kernel(GwIndexView ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
@@ -526,12 +673,26 @@ void gwk_fused(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const
     gw_fused_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, fp, n_active_dev);
 }
 void gwk_pool(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-              uint32_t budget, uint32_t tail_thr, uint32_t cap, uint32_t taper, uint32_t blocks, uint32_t* leftover, uint32_t* leftover_count) {
+              uint32_t budget, uint32_t tail_thr, uint32_t cap, uint32_t taper, uint32_t blocks, uint32_t* leftover, uint32_t* leftover_count, int maxh) {
     if (!n_active) return;
     GwPoolParams pp;
+    pp.batch = pp.age = pp.flush = 1;
     pp.taper = taper;
     pp.budget = budget; pp.tail_thr = tail_thr; pp.cap = cap < 1 ? 1 : (cap > GW_POOL ? GW_POOL : cap);
-    gw_pool_kernel<<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
+    if (maxh <= 4) gw_pool_kernel<4><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
+    else if (maxh <= 8) gw_pool_kernel<8><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
+    else gw_pool_kernel<GW_MAX_ROWS><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
+}
+void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
+              uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh) {
+    if (!n_active) return;
+    GwPoolParams pp;
+    pp.taper = 0; pp.budget = 0; pp.tail_thr = 0;
+    pp.cap = fetch < 1 ? 1 : (fetch > 32 ? 32 : fetch);
+    pp.batch = batch < 1 ? 1 : batch; pp.age = age < 1 ? 1 : age; pp.flush = flush < 1 ? 1 : flush;
+    if (maxh <= 4) gw_flow_kernel<4><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
+    else if (maxh <= 8) gw_flow_kernel<8><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
+    else gw_flow_kernel<GW_MAX_ROWS><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
 }
 void gwk_locate(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
     if (n) gw_locate_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, slabs, req, n);

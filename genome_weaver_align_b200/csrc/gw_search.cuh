@@ -50,6 +50,30 @@ GW_HD u64 gw_state_key(const GwSlab& s, const GwDevConfig& cfg, int32_t off) {
     const int score = gw_score(s, cfg, o, false);
     return ((u64)(uint32_t)gw_priority(o) << 44) | ((u64)(uint32_t)(0x8000000 - score) << 16) | (u64)(uint32_t)(0xFFFF - gw_processed(o));
 }
+// the same key for a state without split chain, from a register copy (a state that was just built need not be read back)
+GW_HD u64 gw_state_key_single(const GwDevConfig& cfg, const GwState* o) {
+    const int nm = gw_lower_k(o);
+    const int score = (gw_processed(o) - nm) * cfg.match_score - nm * cfg.mismatch_penalty;
+    return ((u64)(uint32_t)gw_priority(o) << 44) | ((u64)(uint32_t)(0x8000000 - score) << 16) | (u64)(uint32_t)(0xFFFF - gw_processed(o));
+}
+// java.util.PriorityQueue.offer (siftUp) with the entry's key given; returns false on capacity overflow
+GW_HD bool gw_queue_add_key(const GwSlab& s, int32_t e, const u64 ke) {
+    GwReadCtx* c = s.ctx();
+    int32_t* q = s.queue();
+    u64* qk = s.queue_keys();
+    int k = c->qn;
+    if ((uint32_t)k >= s.sp.queue_cap) return false;
+    c->qn = k + 1;
+    while (k > 0) {
+        const int parent = (k - 1) >> 1;
+        const u64 kp = qk[parent];
+        if (ke >= kp) break;
+        q[k] = q[parent]; qk[k] = kp;
+        k = parent;
+    }
+    q[k] = e; qk[k] = ke;
+    return true;
+}
 // java.util.PriorityQueue.offer (siftUp) ; returns false on capacity overflow
 GW_HD bool gw_queue_add(const GwSlab& s, const GwDevConfig& cfg, int32_t e) {
     if (e < 0) return true;  // StateQueue.add(null) is a no-op
@@ -158,17 +182,22 @@ GW_HD void gw_next_si(const GwIndexView& ix, const GwState* c, int ch, GwSiSet* 
     for (int i = 0; i < 4; ++i) { out->sif[i][0] = out->sif[i][1] = 0; out->sib[i][0] = out->sib[i][1] = 0; }
     if (!hasF && !hasB) { out->kind = GW_SI_EMPTY; return; }
     const int fm = hasF ? (strand == 0 ? 1 : 0) : (strand == 0 ? 0 : 1);
-    const uint32_t lb = gw_clampN(ix, hasF ? c->sif[ch][0] : c->sib[ch][0]);
-    const uint32_t ub = gw_clampN(ix, hasF ? c->sif[ch][1] : c->sib[ch][1]);
+    uint32_t f_lb = 0, f_ub = 0, b_lb = 0, b_ub = 0;   // intervals of `ch`, selected without indexing by a run-time value
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        if (i == ch) { f_lb = c->sif[i][0]; f_ub = c->sif[i][1]; b_lb = c->sib[i][0]; b_ub = c->sib[i][1]; }
+    const uint32_t lb = gw_clampN(ix, hasF ? f_lb : b_lb);
+    const uint32_t ub = gw_clampN(ix, hasF ? f_ub : b_ub);
     uint32_t lo[4], hi[4];
-    GwBlk bl = gw_load_block(ix.occ[fm] + (lb >> 7));
+    // both 64 B lines are requested before the first use, so that their misses overlap (the same line twice is one L1 miss)
+    const GwBlk bl = gw_load_block(ix.occ[fm] + (lb >> 7));
+    const GwBlk bu = gw_load_block(ix.occ[fm] + (ub >> 7));
     gw_rank4(bl, lb & 127u, lo);
-    if ((ub >> 7) == (lb >> 7)) gw_rank4(bl, ub & 127u, hi);  // same 64 B line: one load serves both queries
-    else { GwBlk bu = gw_load_block(ix.occ[fm] + (ub >> 7)); gw_rank4(bu, ub & 127u, hi); }
+    gw_rank4(bu, ub & 127u, hi);
     *occ_lookups += 2;
     uint8_t valid = 0;
     uint32_t x = 0;
-    const uint32_t blb = c->sib[ch][0];
+    const uint32_t blb = b_lb;
     for (int i = 0; i < 4; ++i) {
         const uint32_t l = ix.C[fm][i] + lo[i], u = ix.C[fm][i] + hi[i];
         if (hasF) { out->sif[i][0] = l; out->sif[i][1] = u; } else { out->sib[i][0] = l; out->sib[i][1] = u; }
@@ -190,8 +219,11 @@ GW_HD void gw_next_si(const GwIndexView& ix, const GwState* c, int ch, GwSiSet* 
 
 // ReadAlignmentNFA.nextState + SearchState.nextState on a register copy `c` of the current state (rows in `prev`):
 // returns the arena offset of the new state, -1 for "no match" (null), -2 on slab overflow
+// MAXH: compile-time bound of the NFA height (k + 1). For MAXH <= 8 the rows are kept in registers (every loop over rows is
+// unrolled with constant indices); the generic form (MAXH == GW_MAX_ROWS) keeps them in local memory.
+template <int MAXH = GW_MAX_ROWS>
 GW_HD int32_t gw_next_state(const GwSlab& s, const GwState& c, const u64* prev, int ch, const GwSiSet& nextSi,
-                            const u64* sf_tbl, int sf_kk) {
+                            const u64* sf_tbl, int sf_kk, GwState* built) {
     GwReadCtx* ctx = s.ctx();
     const int m_read = ctx->m;
     const int height = c.height;
@@ -201,26 +233,45 @@ GW_HD int32_t gw_next_state(const GwSlab& s, const GwState& c, const u64* prev, 
     const u64 qeq = gw_pattern_mask64(ctx, gw_strand(&c), m_read, gw_is_fwd(&c), gw_next_index(&c), c.pivot, c.cursor, ch, kr);
     const int progressIndex = gw_processed(&c);
     const int fragmentLength = gw_frag_len(&c);
-    u64 next[GW_MAX_ROWS];
+    u64 next[MAXH];
     int minKwithMatch = k + 1, minKwithProgress = k + 1;
     next[0] = (prev[0] & qeq) << 1;
     if (next[0] != 0) { minKwithMatch = 0; minKwithProgress = 0; }
     next[0] &= gw_staircase64(sf_tbl, m_read, sf_kk, kOffset, progressIndex - k);
-#pragma unroll 1
-    for (int i = 1; i < height; ++i) {
-        u64 v = (prev[i] & qeq) << 1;
-        if (minKwithMatch > k && v != 0) minKwithMatch = i;
-        v |= prev[i - 1] | (prev[i - 1] << 1) | (next[i - 1] << 1);
-        v &= gw_staircase64(sf_tbl, m_read, sf_kk, kOffset + i, progressIndex - k);
-        if (minKwithProgress > k && (v & jshl(1ULL, height)) != 0) minKwithProgress = i;
-        next[i] = v;
-    }
     const int mPos = k + fragmentLength - progressIndex;
     int remove = -1;
     bool hasMatch = false;
-    if (mPos < 64) {
-        for (int nm = 0; nm < height; ++nm)
-            if ((next[nm] & jshl(1ULL, mPos)) != 0) { remove = nm; hasMatch = true; break; }
+    if constexpr (MAXH <= 8) {
+#pragma unroll
+        for (int i = 1; i < MAXH; ++i) {
+            if (i < height) {
+                u64 v = (prev[i] & qeq) << 1;
+                if (minKwithMatch > k && v != 0) minKwithMatch = i;
+                v |= prev[i - 1] | (prev[i - 1] << 1) | (next[i - 1] << 1);
+                v &= gw_staircase64(sf_tbl, m_read, sf_kk, kOffset + i, progressIndex - k);
+                if (minKwithProgress > k && (v & jshl(1ULL, height)) != 0) minKwithProgress = i;
+                next[i] = v;
+            } else next[i] = 0ULL;
+        }
+        if (mPos < 64) {
+#pragma unroll
+            for (int nm = 0; nm < MAXH; ++nm)
+                if (nm < height && remove < 0 && (next[nm] & jshl(1ULL, mPos)) != 0) { remove = nm; hasMatch = true; }
+        }
+    } else {
+#pragma unroll 1
+        for (int i = 1; i < height; ++i) {
+            u64 v = (prev[i] & qeq) << 1;
+            if (minKwithMatch > k && v != 0) minKwithMatch = i;
+            v |= prev[i - 1] | (prev[i - 1] << 1) | (next[i - 1] << 1);
+            v &= gw_staircase64(sf_tbl, m_read, sf_kk, kOffset + i, progressIndex - k);
+            if (minKwithProgress > k && (v & jshl(1ULL, height)) != 0) minKwithProgress = i;
+            next[i] = v;
+        }
+        if (mPos < 64) {
+            for (int nm = 0; nm < height; ++nm)
+                if ((next[nm] & jshl(1ULL, mPos)) != 0) { remove = nm; hasMatch = true; break; }
+        }
     }
     if (remove < 0) {
         int minK = minKwithMatch < minKwithProgress ? minKwithMatch : minKwithProgress;
@@ -243,10 +294,15 @@ GW_HD int32_t gw_next_state(const GwSlab& s, const GwState& c, const u64* prev, 
     const bool fwd = d != GW_DIR_B;
     const bool has = fwd ? ((c.si_kind == GW_SI_F || c.si_kind == GW_SI_BD) && ((c.f_valid >> ch) & 1))
                          : ((c.si_kind == GW_SI_B || c.si_kind == GW_SI_BD) && ((c.b_valid >> ch) & 1));
+    uint32_t clb = 0, cub = 0;   // selected without indexing the interval tables by a run-time value
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        if (i == ch) { clb = fwd ? c.sif[i][0] : c.sib[i][0]; cub = fwd ? c.sif[i][1] : c.sib[i][1]; }
     n.has_cur = has ? 1 : 0;
-    n.cur_lb = has ? (fwd ? c.sif[ch][0] : c.sib[ch][0]) : 0;
-    n.cur_ub = has ? (fwd ? c.sif[ch][1] : c.sib[ch][1]) : 0;
+    n.cur_lb = has ? clb : 0;
+    n.cur_ub = has ? cub : 0;
     n.si_kind = nextSi.kind; n.f_valid = nextSi.f_valid; n.b_valid = nextSi.b_valid;
+#pragma unroll
     for (int i = 0; i < 4; ++i) {
         n.sif[i][0] = nextSi.sif[i][0]; n.sif[i][1] = nextSi.sif[i][1];
         n.sib[i][0] = nextSi.sib[i][0]; n.sib[i][1] = nextSi.sib[i][1];
@@ -255,9 +311,17 @@ GW_HD int32_t gw_next_state(const GwSlab& s, const GwState& c, const u64* prev, 
     n.state = gw_pack_state(ch, kOffset + remove, gw_priority(&c), hasMatch);
     n.next_split = c.next_split;
     *gw_st(s, off) = n;
+    *built = n;
     u64* nr = gw_rows(gw_st(s, off));
-    if (remove == 0) { for (int h = 0; h < newHeight; ++h) nr[h] = prev[h]; }  // sic: the OLD automaton (ReadAlignmentNFA.java:206-207)
-    else { for (int h = 0; h < newHeight; ++h) nr[h] = next[h + remove] >> 1; }
+    if constexpr (MAXH <= 8) {
+        // remove == 0 keeps the OLD automaton (sic, ReadAlignmentNFA.java:206-207)
+#pragma unroll
+        for (int j = 0; j < MAXH; ++j)
+            if (j >= remove && j < height) nr[j - remove] = remove == 0 ? prev[j] : (next[j] >> 1);
+    } else {
+        if (remove == 0) { for (int h = 0; h < newHeight; ++h) nr[h] = prev[h]; }  // sic: the OLD automaton (ReadAlignmentNFA.java:206-207)
+        else { for (int h = 0; h < newHeight; ++h) nr[h] = next[h + remove] >> 1; }
+    }
     return off;
 }
 

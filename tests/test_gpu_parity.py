@@ -193,7 +193,9 @@ def test_sam_parity_scalar_scan_and_small_slab(small):
 
 
 @pytest.mark.parametrize("opts", [dict(fused=0), dict(fused=0, tail_steps=3), dict(fused=1, q_lf=1, q_cols=1), dict(fused=1, q_lf=7, q_cols=33),
-                                  dict(fused=2, pool_budget=3, pool_tail=0), dict(fused=2, pool_tail=1024), dict(fused=2, pool_budget=1000, pool_blocks=1)])
+                                  dict(fused=2, pool_budget=3, pool_tail=0), dict(fused=2, pool_tail=1024), dict(fused=2, pool_budget=1000, pool_blocks=1), dict(fused=2),
+                                  dict(fused=3, flow_batch=1, flow_age=1), dict(fused=3, flow_batch=32, flow_age=1000, flow_flush=32),
+                                  dict(fused=3, flow_fetch=1, flow_flush=1, pool_blocks=3), dict(fused=3, pool_blocks=1)])
 def test_sam_parity_round_mode_and_slice_sizes(small, opts):
     # the round-based kernels (search / locate / verify launched per round) and the fused lane program must agree with the oracle
     # whatever the slice sizes are
