@@ -226,3 +226,41 @@ GW_HD void gw_emit_write(u64* slab_base, const GwDevConfig& cfg, uint32_t read_i
         }
     }
 }
+
+// ---- settle ----------------------------------------------------------------------------------------------
+// When the reads that need a large work area do not fit the memory budget at once, they are run in chunks that share one buffer.
+// After a chunk, the outcome of each read (context with status and counters + the chains that will be reported) is written back
+// into the read's own small work area, which emit reads later; the large area is then free for the next chunk.
+// A read whose reported chains do not fit the small area (ALLHITS with very many hits) ends as GW_ST_UNSUPPORTED.
+GW_HD void gw_settle(u64* big_base, u64* small_base, const GwSlabParams& small_sp, const GwDevConfig& cfg) {
+    GwSlab big(big_base);
+    const GwReadCtx* bc = big.ctx();
+    GwSlab sm(small_base, small_sp);
+    GwReadCtx* sc = sm.ctx();
+    for (uint32_t i = 0; i < GW_CTX_WORDS; ++i) small_base[i] = big_base[i];
+    sc->sp = small_sp;
+    sc->qn = 0;
+    sc->top = (int32_t)sm.arena_begin();
+    const int nrep = gw_num_reported(bc, cfg);
+    sc->n_hits = 0;
+    if (nrep == 0) return;
+    if ((uint32_t)nrep > small_sp.hit_cap) { sc->status = GW_ST_UNSUPPORTED; return; }
+    const int32_t* bh = big.hits();
+    int32_t* sh = sm.hits();
+    for (int i = 0; i < nrep; ++i) {
+        int32_t prev = -1;
+        for (int32_t o = bh[i]; o >= 0; o = gw_hit(big, o)->next_split) {
+            const GwHitNode* h = gw_hit(big, o);
+            const uint32_t words = GW_HIT_WORDS + (uint32_t)((h->cig_n + 1) / 2);
+            const int32_t n = gw_alloc(sm, words);
+            if (n < 0) { sc->n_hits = 0; sc->status = GW_ST_UNSUPPORTED; return; }
+            const u64* src = big.at(o);
+            u64* dst = sm.at(n);
+            for (uint32_t w = 0; w < words; ++w) dst[w] = src[w];
+            gw_hit(sm, n)->next_split = -1;
+            if (prev < 0) sh[i] = n; else gw_hit(sm, prev)->next_split = n;
+            prev = n;
+        }
+    }
+    sc->n_hits = nrep;
+}

@@ -13,6 +13,7 @@
 
 #include "gw_fused.cuh"
 #include "gw_kernels.h"
+#include <stdlib.h>
 
 #define GW_SEARCH_THREADS 64
 
@@ -381,7 +382,7 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(
 //     the reads whose fragments are all done go back to the ready FIFO.
 // There is no per-round tail: a lane that parks or finishes a read takes the next one at once, and locate / DP always run with
 // (nearly) full warps.
-#define GW_RING 256
+#define GW_RING 128     // entries per FIFO; a warp owns at most GW_RING reads (refill stops above GW_RING - 32), at most 95 fragments wait
 #define GW_WARPS (GW_POOL_THREADS / 32)
 template <int MAXH>
 __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
@@ -396,7 +397,7 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const GwRoundQueues noq = gw_no_queues();
-    uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_pick = 0, age_cold = 0;
+    uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_pick = 0, age_cold = 0, owned = 0;
     bool drained = false;
     bool have = false;
     GwSlab s;
@@ -445,7 +446,7 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
             if ((uint32_t)__popc(idle) >= pp.batch || busy == 0u || ++age_pick >= pp.age) {
                 age_pick = 0;
                 uint32_t nrd = n_ready;
-                if (nrd < (uint32_t)__popc(idle) && !drained) {
+                if (nrd < (uint32_t)__popc(idle) && !drained && owned + pp.cap <= GW_RING) {
                     uint32_t first = 0;
                     if (lane == 0) first = atomicAdd(work_counter, pp.cap);
                     first = __shfl_sync(FULL, first, 0);
@@ -453,7 +454,7 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
                     if (first < n_active) got = min(pp.cap, n_active - first);
                     if (first + pp.cap >= n_active) drained = true;
                     if (lane < got) ready[(r_tail + lane) & MASK] = active ? active[first + lane] : first + lane;
-                    r_tail += got; nrd += got;
+                    r_tail += got; nrd += got; owned += got;
                     __syncwarp();
                 }
                 int r0 = -1;
@@ -471,6 +472,7 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
                 const uint32_t pk = __ballot_sync(FULL, r0 == GW_STEP_PARKED);   // exact hit: needs its locate only
                 if (r0 == GW_STEP_PARKED) frags[(f_tail + (uint32_t)__popc(pk & lt)) & MASK] = slot * 2u;
                 f_tail += (uint32_t)__popc(pk);
+                owned -= (uint32_t)__popc(__ballot_sync(FULL, r0 == GW_STEP_DONE));
                 __syncwarp();
                 continue;
             }
@@ -509,6 +511,7 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
             f_tail += (uint32_t)__popc(b_f0) + (uint32_t)__popc(b_f1);
             __syncwarp();
         }
+        owned -= (uint32_t)__popc(__ballot_sync(FULL, have && r == GW_STEP_DONE));
         if (have && r != GW_STEP_CONTINUE) have = false;
     }
 }
@@ -535,6 +538,14 @@ __global__ void gw_collect_overflow_kernel(u64* const* slabs, uint32_t n, uint32
     if (c->status == GW_ST_OVERFLOW) list[atomicAdd(count, 1u)] = i;
 }
 
+__global__ void gw_settle_kernel(u64** slabs, u64* small_base, size_t small_words, GwSlabParams small_sp, const uint32_t* list, uint32_t n, GwDevConfig cfg) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t slot = list[i];
+    u64* sm = small_base + (size_t)slot * small_words;
+    gw_settle(slabs[slot], sm, small_sp, cfg);
+    slabs[slot] = sm;
+}
 __global__ void gw_emit_count_kernel(u64* const* slabs, uint32_t n, GwDevConfig cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long v[7] = {0, 0, 0, 0, 0, 0, 0};
@@ -679,6 +690,14 @@ void gwk_pool(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const 
     pp.batch = pp.age = pp.flush = 1;
     pp.taper = taper;
     pp.budget = budget; pp.tail_thr = tail_thr; pp.cap = cap < 1 ? 1 : (cap > GW_POOL ? GW_POOL : cap);
+    static bool carved = false;   // the lists need 17 KB per CTA: leave the rest of the SM's 256 KB to the L1 (per-read work areas)
+    if (!carved) {
+        const int pct = getenv("GW_CARVEOUT") ? atoi(getenv("GW_CARVEOUT")) : 28;
+        cudaFuncSetAttribute(gw_pool_kernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        cudaFuncSetAttribute(gw_pool_kernel<8>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        cudaFuncSetAttribute(gw_pool_kernel<GW_MAX_ROWS>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        carved = true;
+    }
     if (maxh <= 4) gw_pool_kernel<4><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
     else if (maxh <= 8) gw_pool_kernel<8><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
     else gw_pool_kernel<GW_MAX_ROWS><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
@@ -690,6 +709,14 @@ void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const 
     pp.taper = 0; pp.budget = 0; pp.tail_thr = 0;
     pp.cap = fetch < 1 ? 1 : (fetch > 32 ? 32 : fetch);
     pp.batch = batch < 1 ? 1 : batch; pp.age = age < 1 ? 1 : age; pp.flush = flush < 1 ? 1 : flush;
+    static bool carved = false;   // two CTAs need 18 KB for their FIFOs: the smallest fitting configuration leaves 224 KB of L1
+    if (!carved) {
+        const int pct = getenv("GW_CARVEOUT") ? atoi(getenv("GW_CARVEOUT")) : 14;
+        cudaFuncSetAttribute(gw_flow_kernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        cudaFuncSetAttribute(gw_flow_kernel<8>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        cudaFuncSetAttribute(gw_flow_kernel<GW_MAX_ROWS>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        carved = true;
+    }
     if (maxh <= 4) gw_flow_kernel<4><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
     else if (maxh <= 8) gw_flow_kernel<8><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
     else gw_flow_kernel<GW_MAX_ROWS><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
@@ -702,6 +729,9 @@ void gwk_verify(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const
 }
 void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count) {
     if (n) gw_collect_overflow_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, list, count);
+}
+void gwk_settle(cudaStream_t st, u64** slabs, u64* small_base, size_t small_words, const GwSlabParams& small_sp, const uint32_t* list, uint32_t n, const GwDevConfig& cfg) {
+    if (n) gw_settle_kernel<<<gw_grid(n, 128), 128, 0, st>>>(slabs, small_base, small_words, small_sp, list, n, cfg);
 }
 void gwk_emit_count(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals) {
     if (n) gw_emit_count_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, cfg, n_rec, n_cig, totals);

@@ -192,6 +192,14 @@ def test_sam_parity_scalar_scan_and_small_slab(small):
     compare(small["idx"], small["oidx"], reads, gw.AlignmentConfig(k=3), dict(k=3), scan_coop=0, slab_words=1024, wave_reads=400)
 
 
+def test_sam_parity_large_work_areas_in_chunks(small):
+    # reads that need a large work area share a buffer of tier_budget bytes: with a tiny budget they run in many chunks and their
+    # outcomes are written back to the small work areas between chunks
+    reads = synth.simulate_reads(small["g"], 1500, 100, 3, 79)
+    compare(small["idx"], small["oidx"], reads, gw.AlignmentConfig(k=3), dict(k=3), slab_words=1024, tier_budget_mb=1)
+    compare(small["idx"], small["oidx"], reads, gw.AlignmentConfig(k=3), dict(k=3), slab_words=768, tier_budget_mb=1, fused=3)
+
+
 @pytest.mark.parametrize("opts", [dict(fused=0), dict(fused=0, tail_steps=3), dict(fused=1, q_lf=1, q_cols=1), dict(fused=1, q_lf=7, q_cols=33),
                                   dict(fused=2, pool_budget=3, pool_tail=0), dict(fused=2, pool_tail=1024), dict(fused=2, pool_budget=1000, pool_blocks=1), dict(fused=2),
                                   dict(fused=3, flow_batch=1, flow_age=1), dict(fused=3, flow_batch=32, flow_age=1000, flow_flush=32),
