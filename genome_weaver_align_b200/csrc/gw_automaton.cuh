@@ -317,8 +317,9 @@ GW_HD int gw_search_try(const GwSearchEnv& env, const GwSlab& s, GwSearchLane& L
         }
     }
     GwSiSet nsi;
-    gw_next_si(env.ix, &C, ch, &nsi, &c->occ_search);
-    c->n_fm++;
+    uint32_t lookups = 0;
+    gw_next_si(env.ix, &C, ch, &nsi, &lookups);
+    c->n_fm++;   // every bidirectionalSearch is two rank queries: occ_search is derived as 2 * n_fm when the read is emitted
     GwState built;
     const int32_t ns = gw_next_state<MAXH>(s, C, prev, ch, nsi, tbl, kk, &built);
     if (ns == -2) { Cp->state = flags; gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }

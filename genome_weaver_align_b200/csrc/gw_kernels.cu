@@ -553,7 +553,7 @@ __global__ void gw_emit_count_kernel(u64* const* slabs, uint32_t n, GwDevConfig 
         gw_emit_count(slabs[i], cfg, &n_rec[i], &n_cig[i]);
         const GwReadCtx* c = reinterpret_cast<const GwReadCtx*>(slabs[i]);
         v[0] = (unsigned long long)c->n_fm; v[1] = (unsigned long long)c->n_sw; v[2] = (unsigned long long)c->n_cut; v[3] = (unsigned long long)c->n_filt;
-        v[4] = c->occ_scan; v[5] = c->occ_search; v[6] = c->occ_locate;
+        v[4] = c->occ_scan; v[5] = 2u * (uint32_t)c->n_fm; v[6] = c->occ_locate;
     }
 #pragma unroll
     for (int j = 0; j < 7; ++j) {

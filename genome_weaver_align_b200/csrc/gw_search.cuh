@@ -59,64 +59,52 @@ GW_HD u64 gw_state_key_single(const GwDevConfig& cfg, const GwState* o) {
 // java.util.PriorityQueue.offer (siftUp) with the entry's key given; returns false on capacity overflow
 GW_HD bool gw_queue_add_key(const GwSlab& s, int32_t e, const u64 ke) {
     GwReadCtx* c = s.ctx();
-    int32_t* q = s.queue();
-    u64* qk = s.queue_keys();
+    GwQEntry* q = s.queue();
     int k = c->qn;
     if ((uint32_t)k >= s.sp.queue_cap) return false;
     c->qn = k + 1;
     while (k > 0) {
         const int parent = (k - 1) >> 1;
-        const u64 kp = qk[parent];
-        if (ke >= kp) break;
-        q[k] = q[parent]; qk[k] = kp;
+        const GwQEntry p = q[parent];
+        if (ke >= p.key) break;
+        q[k] = p;
         k = parent;
     }
-    q[k] = e; qk[k] = ke;
+    GwQEntry n;
+    n.key = ke; n.off = e; n.pad_ = 0;
+    q[k] = n;
     return true;
 }
 // java.util.PriorityQueue.offer (siftUp) ; returns false on capacity overflow
 GW_HD bool gw_queue_add(const GwSlab& s, const GwDevConfig& cfg, int32_t e) {
     if (e < 0) return true;  // StateQueue.add(null) is a no-op
-    GwReadCtx* c = s.ctx();
-    int32_t* q = s.queue();
-    u64* qk = s.queue_keys();
-    int k = c->qn;
-    if ((uint32_t)k >= s.sp.queue_cap) return false;
-    c->qn = k + 1;
-    const u64 ke = gw_state_key(s, cfg, e);
-    while (k > 0) {
-        const int parent = (k - 1) >> 1;
-        const u64 kp = qk[parent];
-        if (ke >= kp) break;
-        q[k] = q[parent]; qk[k] = kp;
-        k = parent;
-    }
-    q[k] = e; qk[k] = ke;
-    return true;
+    return gw_queue_add_key(s, e, gw_state_key(s, cfg, e));
 }
 // java.util.PriorityQueue.poll (siftDown)
 GW_HD int32_t gw_queue_poll(const GwSlab& s, const GwDevConfig& cfg) {
     (void)cfg;
     GwReadCtx* c = s.ctx();
-    int32_t* q = s.queue();
-    u64* qk = s.queue_keys();
+    GwQEntry* q = s.queue();
     const int n = --c->qn;
-    const int32_t result = q[0];
-    const int32_t x = q[n];
-    const u64 kx = qk[n];
+    const int32_t result = q[0].off;
+#if defined(__CUDA_ARCH__)
+    // the caller reads this state next: request its line now, the sift-down below hides the latency
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(s.at(result)));
+#endif
     if (n != 0) {
+        const GwQEntry x = q[n];
         int k = 0;
         const int half = n >> 1;
         while (k < half) {
             int child = (k << 1) + 1;
-            u64 kc = qk[child];
             const int right = child + 1;
-            if (right < n) { const u64 kr = qk[right]; if (kc > kr) { kc = kr; child = right; } }
-            if (kx <= kc) break;
-            q[k] = q[child]; qk[k] = kc;
+            GwQEntry cc = q[child];
+            if (right < n) { const GwQEntry cr = q[right]; if (cc.key > cr.key) { cc = cr; child = right; } }
+            if (x.key <= cc.key) break;
+            q[k] = cc;
             k = child;
         }
-        q[k] = x; qk[k] = kx;
+        q[k] = x;
     }
     return result;
 }

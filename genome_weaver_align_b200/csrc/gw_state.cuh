@@ -55,7 +55,13 @@ struct GwReadCtx {
 };
 
 #define GW_CTX_WORDS ((uint32_t)((sizeof(GwReadCtx) + 7) / 8))
-#define GW_MASK_WORDS 0u
+#define GW_QUEUE_BASE ((GW_CTX_WORDS + 1u) & ~1u)   // 16-byte aligned
+
+struct alignas(16) GwQEntry {
+    u64 key;
+    int32_t off;
+    int32_t pad_;
+};
 
 struct GwSlab {
     u64* base;
@@ -64,12 +70,11 @@ struct GwSlab {
     GW_HD explicit GwSlab(u64* b) : base(b) { sp = reinterpret_cast<GwReadCtx*>(b)->sp; }
     GW_HD GwSlab(u64* b, const GwSlabParams& p) : base(b), sp(p) {}
     GW_HD GwReadCtx* ctx() const { return reinterpret_cast<GwReadCtx*>(base); }
-    GW_HD u64* masks() const { return base + GW_CTX_WORDS; }
-    // priority queue: sort keys (comparator of StateQueue packed into one integer, cached at insertion) and state offsets
-    GW_HD u64* queue_keys() const { return base + GW_CTX_WORDS + GW_MASK_WORDS; }
-    GW_HD int32_t* queue() const { return reinterpret_cast<int32_t*>(base + GW_CTX_WORDS + GW_MASK_WORDS + sp.queue_cap); }
-    GW_HD int32_t* hits() const { return queue() + sp.queue_cap; }
-    GW_HD uint32_t arena_begin() const { return (GW_CTX_WORDS + GW_MASK_WORDS + sp.queue_cap + (sp.queue_cap + sp.hit_cap + 1) / 2 + 1u) & ~1u; }
+    // priority queue: one 16-byte entry per queued state — the sort key (comparator of StateQueue packed into one integer, cached at
+    // insertion) next to the state offset, so that a sift step is ONE 128-bit load per level
+    GW_HD GwQEntry* queue() const { return reinterpret_cast<GwQEntry*>(base + GW_QUEUE_BASE); }
+    GW_HD int32_t* hits() const { return reinterpret_cast<int32_t*>(base + GW_QUEUE_BASE + 2u * sp.queue_cap); }
+    GW_HD uint32_t arena_begin() const { return (GW_QUEUE_BASE + 2u * sp.queue_cap + (sp.hit_cap + 1) / 2 + 1u) & ~1u; }
     GW_HD u64* at(int32_t off) const { return base + off; }
 };
 

@@ -15,6 +15,11 @@ sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(
 import oracle_lib
 
 
+def stage(msg, _t=[time.time()]):
+    sys.stderr.write("[scale_check %7.1fs] %s\n" % (time.time() - _t[0], msg))
+    sys.stderr.flush()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--genome-bp", type=int, default=100_000_000)
@@ -44,19 +49,23 @@ def main():
     fasta = os.path.join(a.dir, "ref_%d.fa" % a.genome_bp)
     synth.write_fasta(fasta, contigs)
     res["synth_s"] = round(time.time() - t0, 1)
+    stage("genome written")
 
     t0 = time.time()
     gw.bwt(fasta)
     res["bwt_s"] = round(time.time() - t0, 1)
+    stage("index built")
     t0 = time.time()
     idx = gw.FMIndexOnGenome.load(fasta)
     res["open_s"] = round(time.time() - t0, 1)
     res["text_size"] = int(idx.textSize())
+    stage("index opened")
 
     t0 = time.time()
     reads = synth.simulate_reads_fast(g, a.reads, a.read_len, a.edits, 13)
     seqs = [bytes(r) for r in reads]
     res["reads_s"] = round(time.time() - t0, 1)
+    stage("reads simulated")
     del g
 
     cfg = gw.AlignmentConfig(k=a.k)
@@ -65,26 +74,40 @@ def main():
         n, v = o.split("=")
         al.set_option(n, int(v))
     al.align(seqs[: min(len(seqs), 20000)])   # warm-up (allocations)
+    stage("warm-up batch aligned")
     t0 = time.time()
     batch = al.align(seqs)
     wall = time.time() - t0
+    stage("batch aligned")
     ms = batch.timing
     res["gpu"] = dict(wall_s=round(wall, 3), device_ms=round(ms[5], 2), reads_per_s=round(a.reads / (ms[5] / 1e3)), family_ms=[round(x, 2) for x in ms[:5]],
                       counters=batch.counters)
     st = batch.status()
     res["status_counts"] = {int(k): int(v) for k, v in zip(*np.unique(np.asarray(st), return_counts=True))}
 
-    # parity of a sample against the oracle on the same index files
+    # parity of a sample against the oracle on the same index files (--sample 0: GPU side only; the oracle needs about 0.5 s per
+    # Mbp to open an index)
     ns = min(a.sample, a.reads)
+    if ns == 0:
+        res["parity"] = "not checked"
+        line = json.dumps(res)
+        print(line)
+        if a.out:
+            with open(a.out, "w") as f:
+                f.write(line + "\n")
+        return 0
     pick = np.linspace(0, a.reads - 1, ns).astype(np.int64)
     names = ["r%d" % i for i in range(a.reads)]
     got = batch.sam_per_read(names)
+    stage("SAM formatted")
     t0 = time.time()
     oidx = oracle_lib.OracleIndex.load(fasta)
     res["oracle_open_s"] = round(time.time() - t0, 1)
+    stage("oracle index opened")
     t0 = time.time()
     ref = oidx.align([names[i] for i in pick], [seqs[i].decode() for i in pick], nthreads=a.threads, k=a.k)
     res["oracle_sample_s"] = round(time.time() - t0, 2)
+    stage("oracle sample aligned")
     res["oracle_reads_per_s"] = round(ns / max(time.time() - t0, 1e-9))
     bad = []
     for j, i in enumerate(pick):
