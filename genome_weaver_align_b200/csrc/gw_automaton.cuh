@@ -219,6 +219,12 @@ GW_COLD int gw_search_report(const GwSearchEnv& env, const GwSlab& s, uint32_t s
 template <bool DEFER = false>
 GW_HD int gw_search_poll(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq, GwSearchLane& L) {
     GwReadCtx* c = s.ctx();
+#if defined(__CUDA_ARCH__)
+    // a step touches, one after the other, the context header, the head of the queue, the polled state and the read's bit planes:
+    // the lines whose addresses are known now are requested together, so that their misses overlap
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(s.queue()));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(&c->qlo[0][0]));
+#endif
     const int m = c->m;
     const GwDevConfig& cfg = env.cfg;
     L.mid = 0;

@@ -25,6 +25,7 @@ struct GwBatchView {
     const char* bases;        // concatenated ASCII reads
     const u64* offsets;       // n+1
     const int32_t* k_by_m;    // [GW_MAX_READ_LEN+1] AlignmentScoreConfig.getMaximumEditDistance(m); -1: unsupported
+    GwExtPool* ext_pool;      // arena extension blocks of this wave, or null
 };
 
 // ---- prep: encode one read into its slab -----------------------------------------------------------------
@@ -34,6 +35,7 @@ GW_HD void gw_prep_read(const GwBatchView& bv, u64* slab_base, const GwSlabParam
     const u64 b0 = bv.offsets[read_id], b1 = bv.offsets[read_id + 1];
     const long long len = (long long)(b1 - b0);
     c->sp = sp;
+    c->ext = nullptr; c->ext_pool = bv.ext_pool;
     c->read_id = (int32_t)read_id;
     c->m = (int32_t)(len > 0x7fffffffLL ? 0x7fffffff : len);
     c->k = 0;
@@ -239,6 +241,7 @@ GW_HD void gw_settle(u64* big_base, u64* small_base, const GwSlabParams& small_s
     GwReadCtx* sc = sm.ctx();
     for (uint32_t i = 0; i < GW_CTX_WORDS; ++i) small_base[i] = big_base[i];
     sc->sp = small_sp;
+    sc->ext = nullptr; sc->ext_pool = nullptr;
     sc->qn = 0;
     sc->top = (int32_t)sm.arena_begin();
     const int nrep = gw_num_reported(bc, cfg);

@@ -90,6 +90,17 @@ struct GwSlabParams {
     uint32_t hit_cap;      // max entries of the hit list
 };
 
+// pool of larger work areas (device memory): a read whose work area is nearly full is moved into ONE block of the pool between two
+// search steps and goes on there, instead of being run again from the start. `next` is the allocation cursor (atomic, reset by
+// the host for every wave).
+struct GwExtPool {
+    u64* base;
+    uint32_t n_blocks;
+    uint32_t block_words;
+    uint32_t next;
+    uint32_t pad_;
+};
+
 // staircase filter tables for every read length present in a batch
 struct GwStaircaseView {
     const u64* words;           // all tables

@@ -299,7 +299,10 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(
                     have = true;
                 }
                 int r = GW_STEP_CONTINUE;
-                if (!L.mid) r = gw_search_poll(env, s, slot, noq, L);
+                if (!L.mid) {
+                    if (gw_wants_promotion(s)) gw_promote(s, const_cast<u64**>(slabs) + slot);   // nearly full: go on in a larger work area
+                    r = gw_search_poll(env, s, slot, noq, L);
+                }
                 if (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try<false, MAXH>(env, s, L);
                 if (r == GW_STEP_CONTINUE) {
                     if (--budget == 0 && !L.mid) { ready[n_idx][atomicAdd(&n_ready[n_idx], 1u)] = slot; have = false; }
@@ -481,7 +484,10 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
         }
         // ---- one search slice per lane
         int r = GW_STEP_CONTINUE;
-        if (have && L.mid == 0) r = gw_search_poll<true>(env, s, slot, noq, L);
+        if (have && L.mid == 0) {
+            if (gw_wants_promotion(s)) gw_promote(s, const_cast<u64**>(slabs) + slot);   // nearly full: go on in a larger work area
+            r = gw_search_poll<true>(env, s, slot, noq, L);
+        }
         if (have && r == GW_STEP_CONTINUE && L.mid == GW_MID_TRY) r = gw_search_try<true, MAXH>(env, s, L);
         // ---- deferred continuations
         {

@@ -38,6 +38,8 @@ struct GwJob {
 };
 
 struct GwReadCtx {
+    u64* ext;              // the larger block this read was moved to while running (gw_promote), or null
+    GwExtPool* ext_pool;   // pool of such blocks, or null
     int32_t m, k;
     int32_t min_mm, max_match_len, best_score;
     int32_t n_fm, n_sw, n_cut, n_filt;
@@ -144,7 +146,7 @@ struct GwHitNode {
 #define GW_HIT_WORDS ((uint32_t)((sizeof(GwHitNode) + 7) / 8))
 GW_HD uint32_t* gw_hit_cigar(GwHitNode* h) { return reinterpret_cast<uint32_t*>(reinterpret_cast<u64*>(h) + GW_HIT_WORDS); }
 
-// bump allocation; returns -1 (and flags the read for the large-slab pass) on overflow
+// bump allocation; returns -1 (and the caller flags the read for the large-slab pass) on overflow
 GW_HD int32_t gw_alloc(const GwSlab& s, uint32_t words) {
     GwReadCtx* c = s.ctx();
     words = (words + 1u) & ~1u;   // nodes stay 16-byte aligned (128-bit loads/stores of whole states)
@@ -152,6 +154,39 @@ GW_HD int32_t gw_alloc(const GwSlab& s, uint32_t words) {
     if (top + words > s.sp.slab_words) return -1;
     c->top = (int32_t)(top + words);
     return (int32_t)top;
+}
+
+// Moving a read to a larger work area while it runs. All references inside a work area are word offsets from its base and the
+// layout in front of the arena (context, queue, hit list) depends on queue_cap / hit_cap only, so a work area can be copied to the
+// start of a larger block and simply go on there with a larger slab_words. This is done between two steps of the best-first loop
+// (no pointer into the old area is live then), when the free space falls below what one step can allocate at most:
+// up to 5 candidate states + 4 states of the split / clip children + 2 hit nodes.
+GW_HD uint32_t gw_step_alloc_bound(int k) {
+    const uint32_t st = (GW_STATE_WORDS + (uint32_t)k + 2u) & ~1u;
+    return 9u * st + 2u * ((GW_HIT_WORDS + GW_CIG_CAP / 2u + 1u) & ~1u);
+}
+GW_HD bool gw_wants_promotion(const GwSlab& s) {
+    const GwReadCtx* c = s.ctx();
+    return (uint32_t)c->top + gw_step_alloc_bound(c->k) > s.sp.slab_words && c->ext_pool != nullptr && c->ext == nullptr;
+}
+// takes one block from the pool, copies the used part of the work area into it and makes it the read's work area; false: no block left
+GW_COLD bool gw_promote(GwSlab& s, u64** slab_ptr) {
+    GwReadCtx* c = s.ctx();
+    GwExtPool* pool = c->ext_pool;
+    const uint32_t idx = gw_atomic_add(&pool->next, 1u);
+    if (idx >= pool->n_blocks || pool->block_words <= s.sp.slab_words) { c->ext_pool = nullptr; return false; }
+    u64* nb = pool->base + (size_t)idx * pool->block_words;
+    const uint32_t top = (uint32_t)c->top;   // even: the arena starts at an even word and nodes are multiples of two words
+    const GwU64x2* src = reinterpret_cast<const GwU64x2*>(s.base);
+    GwU64x2* dst = reinterpret_cast<GwU64x2*>(nb);
+    for (uint32_t i = 0; i < top / 2u; ++i) dst[i] = src[i];
+    GwReadCtx* nc = reinterpret_cast<GwReadCtx*>(nb);
+    nc->sp.slab_words = pool->block_words;
+    nc->ext = nb;   // marks the read as moved (it is not moved twice)
+    *slab_ptr = nb;
+    s.base = nb;
+    s.sp.slab_words = pool->block_words;
+    return true;
 }
 
 // ---- BitVector.substring64 over nb blocks -----------------------------------------------------------------

@@ -98,7 +98,7 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
         }
         env.sf.words = words.data(); env.sf.base_by_m = base.data(); env.sf.abort_by_m = abortm.data();
         GwBatchView bv;
-        bv.bases = bases; bv.offsets = (const u64*)offsets; bv.k_by_m = k_by_m;
+        bv.bases = bases; bv.offsets = (const u64*)offsets; bv.k_by_m = k_by_m; bv.ext_pool = nullptr;
 
         std::vector<std::vector<u64>> slab_store(n_reads);
         std::vector<u64*> slabs(n_reads, nullptr);
