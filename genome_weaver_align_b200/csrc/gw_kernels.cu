@@ -484,10 +484,25 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
         }
         // ---- one search slice per lane
         int r = GW_STEP_CONTINUE;
-        if (have && L.mid == 0) {
-            if (gw_wants_promotion(s)) gw_promote(s, const_cast<u64**>(slabs) + slot);   // nearly full: go on in a larger work area
-            r = gw_search_poll<true>(env, s, slot, noq, L);
+        {   // work areas that are nearly full: the reads go on in a larger one; the lanes of the warp share each copy
+            const bool wantp = have && L.mid == 0 && gw_wants_promotion(s);
+            if (__ballot_sync(FULL, wantp) != 0u) {
+                u64* nb = wantp ? gw_promote_take(s) : nullptr;
+                uint32_t pm = __ballot_sync(FULL, nb != nullptr);
+                const uint32_t my_top = nb ? (uint32_t)s.ctx()->top : 0u;
+                while (pm) {
+                    const int src = __ffs(pm) - 1;
+                    pm &= pm - 1u;
+                    const u64* from = reinterpret_cast<const u64*>(__shfl_sync(FULL, (unsigned long long)s.base, src));
+                    u64* to = reinterpret_cast<u64*>(__shfl_sync(FULL, (unsigned long long)nb, src));
+                    const uint32_t top = __shfl_sync(FULL, my_top, src);
+                    gw_promote_copy(from, to, top, lane, 32u);
+                }
+                __syncwarp();
+                if (nb) gw_promote_commit(s, nb, const_cast<u64**>(slabs) + slot);
+            }
         }
+        if (have && L.mid == 0) r = gw_search_poll<true>(env, s, slot, noq, L);
         if (have && r == GW_STEP_CONTINUE && L.mid == GW_MID_TRY) r = gw_search_try<true, MAXH>(env, s, L);
         // ---- deferred continuations
         {

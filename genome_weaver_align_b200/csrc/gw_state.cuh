@@ -169,23 +169,36 @@ GW_HD bool gw_wants_promotion(const GwSlab& s) {
     const GwReadCtx* c = s.ctx();
     return (uint32_t)c->top + gw_step_alloc_bound(c->k) > s.sp.slab_words && c->ext_pool != nullptr && c->ext == nullptr;
 }
-// takes one block from the pool, copies the used part of the work area into it and makes it the read's work area; false: no block left
-GW_COLD bool gw_promote(GwSlab& s, u64** slab_ptr) {
+// the move in three parts, so that the copy can be shared by the lanes of a warp: take a block from the pool (null: none left) ...
+GW_COLD u64* gw_promote_take(const GwSlab& s) {
     GwReadCtx* c = s.ctx();
     GwExtPool* pool = c->ext_pool;
     const uint32_t idx = gw_atomic_add(&pool->next, 1u);
-    if (idx >= pool->n_blocks || pool->block_words <= s.sp.slab_words) { c->ext_pool = nullptr; return false; }
-    u64* nb = pool->base + (size_t)idx * pool->block_words;
-    const uint32_t top = (uint32_t)c->top;   // even: the arena starts at an even word and nodes are multiples of two words
-    const GwU64x2* src = reinterpret_cast<const GwU64x2*>(s.base);
-    GwU64x2* dst = reinterpret_cast<GwU64x2*>(nb);
-    for (uint32_t i = 0; i < top / 2u; ++i) dst[i] = src[i];
+    if (idx >= pool->n_blocks || pool->block_words <= s.sp.slab_words) { c->ext_pool = nullptr; return nullptr; }
+    return pool->base + (size_t)idx * pool->block_words;
+}
+// ... copy the used part of the work area [0, top) (top is even: the arena starts at an even word, nodes are multiples of two
+// words), `part` of `parts` ...
+GW_HD void gw_promote_copy(const u64* from, u64* to, uint32_t top, uint32_t part, uint32_t parts) {
+    const GwU64x2* src = reinterpret_cast<const GwU64x2*>(from);
+    GwU64x2* dst = reinterpret_cast<GwU64x2*>(to);
+    for (uint32_t i = part; i < top / 2u; i += parts) dst[i] = src[i];
+}
+// ... and make the block the read's work area
+GW_HD void gw_promote_commit(GwSlab& s, u64* nb, u64** slab_ptr) {
     GwReadCtx* nc = reinterpret_cast<GwReadCtx*>(nb);
-    nc->sp.slab_words = pool->block_words;
+    const uint32_t words = nc->ext_pool->block_words;
+    nc->sp.slab_words = words;
     nc->ext = nb;   // marks the read as moved (it is not moved twice)
     *slab_ptr = nb;
     s.base = nb;
-    s.sp.slab_words = pool->block_words;
+    s.sp.slab_words = words;
+}
+GW_COLD bool gw_promote(GwSlab& s, u64** slab_ptr) {
+    u64* nb = gw_promote_take(s);
+    if (!nb) return false;
+    gw_promote_copy(s.base, nb, (uint32_t)s.ctx()->top, 0u, 1u);
+    gw_promote_commit(s, nb, slab_ptr);
     return true;
 }
 
