@@ -247,8 +247,8 @@ def run_ours(args):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-        # Kernel families of one step. Search, locate and verification run inside ONE kernel family (gw_pool_kernel + gw_fused_kernel
-        # for its stragglers), so their lookups are charged to the same CUDA-event time: 64 B per occurrence-table lookup
+        # Kernel families of one step. Search, locate and verification run inside ONE kernel (gw_flow_kernel; further launches of it only
+        # for reads that need a still larger work area), so their lookups are charged to the same CUDA-event time: 64 B per occurrence-table lookup
         # (search: 2 per bidirectional step; locate: 1 per LF step) + 4 B per SA sample.
         fams = {
             "scan": (counters["occ_lookups_scan"] * 64.0, fam_ms[0]),

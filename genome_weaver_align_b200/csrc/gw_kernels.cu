@@ -584,26 +584,61 @@ __global__ void gw_emit_count_kernel(u64* const* slabs, uint32_t n, GwDevConfig 
     }
 }
 
-// single-block exclusive scan of two u32 arrays into u64 offsets (+ base); totals to out_tot[0..1]
-__global__ void gw_scan2_kernel(const uint32_t* a, const uint32_t* b, uint32_t n, unsigned long long base_a, unsigned long long base_b,
-                                unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot) {
-    __shared__ unsigned long long sa[1024], sb[1024];
-    const uint32_t t = threadIdx.x, T = blockDim.x;
-    const uint32_t per = (n + T - 1) / T;
-    const uint32_t lo = min(n, t * per), hi = min(n, lo + per);
+// exclusive scan of two u32 arrays into u64 offsets (+ base), totals to out_tot[0..1], in three launches: per-block sums of chunks
+// of `chunk` elements (a multiple of the block size, at most 1024 chunks), a single-block scan of those sums, and the scan inside
+// every chunk. All loads and stores are coalesced.
+#define GW_SCAN_T 256
+__device__ __forceinline__ void gw_block_sum2(unsigned long long& xa, unsigned long long& xb, unsigned long long* sh) {
+    for (int d = 16; d > 0; d >>= 1) { xa += __shfl_xor_sync(0xFFFFFFFFu, xa, d); xb += __shfl_xor_sync(0xFFFFFFFFu, xb, d); }
+    const uint32_t w = threadIdx.x >> 5, l = threadIdx.x & 31u;
+    if (l == 0) { sh[w] = xa; sh[8 + w] = xb; }
+    __syncthreads();
+    xa = 0; xb = 0;
+    for (uint32_t i = 0; i < GW_SCAN_T / 32; ++i) { xa += sh[i]; xb += sh[8 + i]; }
+}
+__global__ void __launch_bounds__(GW_SCAN_T) gw_scan2_partial_kernel(const uint32_t* a, const uint32_t* b, uint32_t n, uint32_t chunk,
+                                                                      unsigned long long* pa, unsigned long long* pb) {
+    __shared__ unsigned long long sh[16];
+    const uint32_t lo = blockIdx.x * chunk, hi = min(n, lo + chunk);
     unsigned long long xa = 0, xb = 0;
-    for (uint32_t i = lo; i < hi; ++i) { xa += a[i]; xb += b[i]; }
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += GW_SCAN_T) { xa += a[i]; xb += b[i]; }
+    gw_block_sum2(xa, xb, sh);
+    if (threadIdx.x == 0) { pa[blockIdx.x] = xa; pb[blockIdx.x] = xb; }
+}
+__global__ void __launch_bounds__(1024) gw_scan2_offsets_kernel(unsigned long long* pa, unsigned long long* pb, uint32_t nb, unsigned long long base_a,
+                                                                 unsigned long long base_b, unsigned long long* out_tot) {
+    __shared__ unsigned long long sa[1024], sb[1024];
+    const uint32_t t = threadIdx.x;
+    const unsigned long long xa = t < nb ? pa[t] : 0, xb = t < nb ? pb[t] : 0;
     sa[t] = xa; sb[t] = xb;
     __syncthreads();
-    for (uint32_t d = 1; d < T; d <<= 1) {
-        unsigned long long ya = t >= d ? sa[t - d] : 0, yb = t >= d ? sb[t - d] : 0;
+    for (uint32_t d = 1; d < 1024; d <<= 1) {
+        const unsigned long long ya = t >= d ? sa[t - d] : 0, yb = t >= d ? sb[t - d] : 0;
         __syncthreads();
         sa[t] += ya; sb[t] += yb;
         __syncthreads();
     }
-    unsigned long long pa = base_a + sa[t] - xa, pb = base_b + sb[t] - xb;
-    for (uint32_t i = lo; i < hi; ++i) { oa[i] = pa; ob[i] = pb; pa += a[i]; pb += b[i]; }
-    if (t == T - 1) { out_tot[0] = sa[t]; out_tot[1] = sb[t]; }
+    if (t < nb) { pa[t] = base_a + sa[t] - xa; pb[t] = base_b + sb[t] - xb; }
+    if (t == 1023) { out_tot[0] = sa[t]; out_tot[1] = sb[t]; }
+}
+__global__ void __launch_bounds__(GW_SCAN_T) gw_scan2_final_kernel(const uint32_t* a, const uint32_t* b, uint32_t n, uint32_t chunk,
+                                                                    const unsigned long long* pa, const unsigned long long* pb,
+                                                                    unsigned long long* oa, unsigned long long* ob) {
+    __shared__ unsigned long long sa[GW_SCAN_T], sb[GW_SCAN_T];
+    const uint32_t t = threadIdx.x, per = chunk / GW_SCAN_T;
+    const uint32_t lo = min(n, blockIdx.x * chunk + t * per), hi = min(n, lo + per);
+    unsigned long long xa = 0, xb = 0;
+    for (uint32_t i = lo; i < hi; ++i) { xa += a[i]; xb += b[i]; }
+    sa[t] = xa; sb[t] = xb;
+    __syncthreads();
+    for (uint32_t d = 1; d < GW_SCAN_T; d <<= 1) {
+        const unsigned long long ya = t >= d ? sa[t - d] : 0, yb = t >= d ? sb[t - d] : 0;
+        __syncthreads();
+        sa[t] += ya; sb[t] += yb;
+        __syncthreads();
+    }
+    unsigned long long qa = pa[blockIdx.x] + sa[t] - xa, qb = pb[blockIdx.x] + sb[t] - xb;
+    for (uint32_t i = lo; i < hi; ++i) { oa[i] = qa; ob[i] = qb; qa += a[i]; qb += b[i]; }
 }
 
 __global__ void gw_emit_write_kernel(u64* const* slabs, uint32_t n, GwDevConfig cfg, uint32_t read_base, const unsigned long long* rec_off,
@@ -758,8 +793,14 @@ void gwk_emit_count(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevC
     if (n) gw_emit_count_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, cfg, n_rec, n_cig, totals);
 }
 void gwk_scan2(cudaStream_t st, const uint32_t* a, const uint32_t* b, uint32_t n, unsigned long long base_a, unsigned long long base_b,
-               unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot) {
-    gw_scan2_kernel<<<1, 1024, 0, st>>>(a, b, n, base_a, base_b, oa, ob, out_tot);
+               unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot, unsigned long long* part) {
+    if (!n) { gw_scan2_offsets_kernel<<<1, 1024, 0, st>>>(part, part + 1024, 0, base_a, base_b, out_tot); return; }
+    uint32_t chunk = (n + 1023) / 1024;
+    chunk = (chunk + GW_SCAN_T - 1) / GW_SCAN_T * GW_SCAN_T;
+    const uint32_t nb = (n + chunk - 1) / chunk;
+    gw_scan2_partial_kernel<<<nb, GW_SCAN_T, 0, st>>>(a, b, n, chunk, part, part + 1024);
+    gw_scan2_offsets_kernel<<<1, 1024, 0, st>>>(part, part + 1024, nb, base_a, base_b, out_tot);
+    gw_scan2_final_kernel<<<nb, GW_SCAN_T, 0, st>>>(a, b, n, chunk, part, part + 1024, oa, ob);
 }
 void gwk_emit_write(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t read_base, const unsigned long long* rec_off,
                     const unsigned long long* cig_off, void* recs, unsigned long long rec_cap, uint32_t* cigs, unsigned long long cig_cap) {

@@ -21,7 +21,7 @@ void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32
 void gwk_settle(cudaStream_t st, u64** slabs, u64* small_base, size_t small_words, const GwSlabParams& small_sp, const uint32_t* list, uint32_t n, const GwDevConfig& cfg);
 void gwk_emit_count(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals);
 void gwk_scan2(cudaStream_t st, const uint32_t* a, const uint32_t* b, uint32_t n, unsigned long long base_a, unsigned long long base_b,
-               unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot);
+               unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot, unsigned long long* part /* 2048 words of scratch */);
 void gwk_emit_write(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t read_base, const unsigned long long* rec_off,
                     const unsigned long long* cig_off, void* recs, unsigned long long rec_cap, uint32_t* cigs, unsigned long long cig_cap);
 void gwk_gather_bench(cudaStream_t st, const GwIndexView& ix, int which, uint32_t blocks, uint32_t per_thread, uint32_t seed, uint32_t* sink);
