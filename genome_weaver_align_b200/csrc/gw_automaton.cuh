@@ -105,13 +105,21 @@ GW_COLD void gw_finish_report(const GwSearchEnv& env, const GwSlab& s) {
     if (!gw_add_result(s, env.cfg, first)) gw_fail(c, GW_ST_OVERFLOW);
 }
 
-// staircase table of the current minMismatches; returns nullptr and fails the read where the reference constructor throws
+// staircase table of the current minMismatches; returns nullptr and fails the read where the reference constructor throws.
+// The table only changes when minMismatches does (a reported hit), so its offset is kept in the context: the usual call reads
+// three words of the context header instead of walking m -> abort bitmap -> table base.
 GW_HD const u64* gw_staircase_for(const GwSearchEnv& env, GwReadCtx* c, int* kk) {
-    const int m = c->m, mm = c->min_mm;
+    const int mm = c->min_mm;
     *kk = mm;
-    if (mm < 0 || ((env.sf.abort_by_m[m] >> mm) & 1u)) { gw_fail(c, GW_ST_ABORT); return nullptr; }
-    const int nb = (m + 63) >> 6;
-    return env.sf.words + env.sf.base_by_m[m] + nb * (mm * (mm + 1) / 2);
+    if (c->sf_mm != mm) {
+        const int m = c->m;
+        int off = -1;
+        if (mm >= 0 && !((env.sf.abort_by_m[m] >> mm) & 1u)) off = env.sf.base_by_m[m] + ((m + 63) >> 6) * (mm * (mm + 1) / 2);
+        c->sf_mm = mm; c->sf_off = off;
+    }
+    const int off = c->sf_off;
+    if (off < 0) { gw_fail(c, GW_ST_ABORT); return nullptr; }
+    return env.sf.words + off;
 }
 
 // ---- resumable driver ------------------------------------------------------------------------------------
@@ -310,6 +318,14 @@ GW_HD int gw_search_try(const GwSearchEnv& env, const GwSlab& s, GwSearchLane& L
         L.mid = 0;
         return gw_search_split(env, s, L);
     }
+#if defined(__CUDA_ARCH__)
+    {   // the new state will be sifted up from the end of the queue: request the lines of its parent and grandparent
+        const int qn = c->qn;
+        const GwQEntry* q = s.queue();
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(q + ((qn - 1) >> 1)));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(q + ((((qn - 1) >> 1) - 1) >> 1)));
+    }
+#endif
     int kk;
     const u64* tbl = gw_staircase_for(env, c, &kk);
     u64 prev[MAXH];
@@ -334,7 +350,14 @@ GW_HD int gw_search_try(const GwSearchEnv& env, const GwSlab& s, GwSearchLane& L
         const bool ok = (L.c_off == L.base && built.next_split < 0) ? gw_queue_add_key(s, ns, gw_state_key_single(cfg, &built))
                                                                     : gw_queue_add(s, cfg, gw_update(s, L.base, L.c_off, ns));
         if (!ok) { Cp->state = flags; gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
-        if (own) { Cp->state = flags; L.mid = 0; return GW_STEP_CONTINUE; }   // extended: the parent is dropped (:426-429)
+        if (own) {   // extended: the parent is dropped (:426-429)
+            Cp->state = flags; L.mid = 0;
+#if defined(__CUDA_ARCH__)
+            // the step is over: the head of the queue is polled next; request its state now
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(s.at(s.queue()[0].off)));
+#endif
+            return GW_STEP_CONTINUE;
+        }
     } else
         c->n_filt++;
     Cp->state = flags;

@@ -44,6 +44,7 @@ GW_HD void gw_prep_read(const GwBatchView& bv, u64* slab_base, const GwSlabParam
     c->qn = 0; c->n_hits = 0;
     c->top = (int32_t)s.arena_begin();
     c->pend_base = -1; c->pend_n = 0;
+    c->sf_mm = -2; c->sf_off = -1;
     c->count_n = 0;
     c->occ_scan = c->occ_search = c->occ_locate = 0;
     c->status = GW_ST_OK;

@@ -48,6 +48,7 @@ struct GwReadCtx {
     int32_t scan_mm[2], scan_ls[2], scan_le[2];
     uint32_t scan_lb[2], scan_ub[2];
     int32_t pend_base, pend_n;
+    int32_t sf_mm, sf_off;    // staircase table of minMismatches == sf_mm: word offset in the table set, -1: the reference throws (cache)
     int32_t count_n, read_id;
     GwSlabParams sp;          // geometry of the slab this context lives in
     uint32_t occ_scan, occ_search, occ_locate;   // occurrence-table lookups done for this read (roofline work unit)
