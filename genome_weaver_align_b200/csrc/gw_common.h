@@ -21,10 +21,10 @@
 #define GW_HD __host__ __device__ __forceinline__
 // rarely executed, large bodies (seeding, reporting, split states, DP set-up, traceback): ONE out-of-line copy keeps the hot loops
 // of the fused kernel small enough for the instruction cache
-#define GW_COLD static __host__ __device__ __noinline__
+#define GW_COLD __attribute__((unused)) static __host__ __device__ __noinline__
 #else
 #define GW_HD inline
-#define GW_COLD static inline
+#define GW_COLD __attribute__((unused)) static inline
 #endif
 
 typedef unsigned long long u64;

@@ -223,16 +223,20 @@ void gw_load_acgt(const std::string& path, std::vector<uint8_t>& codes) {
     const uint64_t groups = (n + 63) / 64;
     if (raw.size() < groups * 24) throw GwIoError("short payload in " + path);
     codes.resize((size_t)n);
-    for (uint64_t g = 0; g < groups; ++g) {
-        uint64_t w[3];
-        memcpy(w, raw.data() + g * 24, 24);
-        const unsigned cnt = (unsigned)std::min<uint64_t>(64, n - g * 64);
-        for (unsigned off = 0; off < cnt; ++off) {
-            const unsigned nf = (unsigned)((w[0] >> (63 - off)) & 1ULL);
-            const unsigned c2 = (unsigned)((w[1 + (off >> 5)] >> (62 - 2 * (off & 31))) & 3ULL);
-            codes[(size_t)(g * 64 + off)] = (uint8_t)(nf ? 4 : c2);
+    uint8_t* out = codes.data();
+    const uint8_t* in = raw.data();
+    gw_parallel_for(groups, gw_host_threads(), [&](uint64_t g0, uint64_t g1, unsigned) {
+        for (uint64_t g = g0; g < g1; ++g) {
+            uint64_t w[3];
+            memcpy(w, in + g * 24, 24);
+            const unsigned cnt = (unsigned)std::min<uint64_t>(64, n - g * 64);
+            for (unsigned off = 0; off < cnt; ++off) {
+                const unsigned nf = (unsigned)((w[0] >> (63 - off)) & 1ULL);
+                const unsigned c2 = (unsigned)((w[1 + (off >> 5)] >> (62 - 2 * (off & 31))) & 3ULL);
+                out[(size_t)(g * 64 + off)] = (uint8_t)(nf ? 4 : c2);
+            }
         }
-    }
+    });
 }
 
 void gw_save_ssa(const std::string& path, uint64_t N, const std::vector<uint32_t>& samples) {
@@ -330,14 +334,24 @@ void gw_load_index_files(const std::string& fasta_path, GwHostIndex& ix) {
     uint64_t total = 0;
     gw_load_silk(p + ".i.silk", ix.contigs, &total);
     ix.N = total;
-    for (int s = 0; s < 2; ++s) {
-        uint64_t n = 0;
-        int L = 0;
-        gw_load_ssa(p + (s == 0 ? ".f.ssa" : ".r.ssa"), &n, &L, ix.ssa[s]);
-        if (L != 32) throw GwIoError("unsupported suffix array sampling (L != 32) in " + p);
-        gw_load_acgt(p + (s == 0 ? ".f.bwt" : ".r.bwt"), ix.bwt[s]);
-        if (ix.bwt[s].size() != ix.N || n != ix.N) throw GwIoError("index files of " + p + " disagree on the text size");
-    }
-    gw_load_acgt(p + ".f.3bit", ix.text);
-    if (ix.text.size() != ix.N) throw GwIoError("reference text of " + p + " disagrees on the text size");
+    // the five files are independent: read and decode them side by side
+    gw_parallel_for(5, 5, [&](uint64_t lo, uint64_t hi, unsigned) {
+        for (uint64_t f = lo; f < hi; ++f) {
+            if (f < 2) {
+                const int s = (int)f;
+                uint64_t n = 0;
+                int L = 0;
+                gw_load_ssa(p + (s == 0 ? ".f.ssa" : ".r.ssa"), &n, &L, ix.ssa[s]);
+                if (L != 32) throw GwIoError("unsupported suffix array sampling (L != 32) in " + p);
+                if (n != ix.N) throw GwIoError("index files of " + p + " disagree on the text size");
+            } else if (f < 4) {
+                const int s = (int)f - 2;
+                gw_load_acgt(p + (s == 0 ? ".f.bwt" : ".r.bwt"), ix.bwt[s]);
+                if (ix.bwt[s].size() != ix.N) throw GwIoError("index files of " + p + " disagree on the text size");
+            } else {
+                gw_load_acgt(p + ".f.3bit", ix.text);
+                if (ix.text.size() != ix.N) throw GwIoError("reference text of " + p + " disagrees on the text size");
+            }
+        }
+    });
 }

@@ -3,6 +3,7 @@
 #pragma once
 #include <stdint.h>
 
+#include <algorithm>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -24,6 +25,26 @@ struct GwHostIndex {
 struct GwIoError : public std::runtime_error {
     explicit GwIoError(const std::string& w) : std::runtime_error(w) {}
 };
+
+// host threads for opening an index (file decoding and laying out the HBM image): fn(lo, hi, part) over [0, n) in `parts` pieces;
+// the first exception thrown by a piece is rethrown in the caller
+#include <exception>
+#include <thread>
+template <typename F>
+inline void gw_parallel_for(uint64_t n, unsigned parts, F fn) {
+    if (parts < 1) parts = 1;
+    if (parts == 1 || n < 2) { fn((uint64_t)0, n, 0u); return; }
+    std::vector<std::thread> th;
+    std::vector<std::exception_ptr> err(parts);
+    const uint64_t per = (n + parts - 1) / parts;
+    for (unsigned t = 0; t < parts; ++t) {
+        const uint64_t lo = std::min<uint64_t>(n, (uint64_t)t * per), hi = std::min<uint64_t>(n, lo + per);
+        th.emplace_back([&, lo, hi, t] { try { fn(lo, hi, t); } catch (...) { err[t] = std::current_exception(); } });
+    }
+    for (auto& x : th) x.join();
+    for (auto& e : err) if (e) std::rethrow_exception(e);
+}
+inline unsigned gw_host_threads() { unsigned h = std::thread::hardware_concurrency(); return h < 1 ? 1 : (h > 32 ? 32 : h); }
 
 // ---- files (gw_files.cpp) ----------------------------------------------------------------------------------
 std::string gw_index_prefix(const std::string& fasta_path);                       // BWTFiles.java:40-47

@@ -31,23 +31,40 @@ inline void gw_layout_index(const GwHostIndex& h, GwIndexImage& img) {
         memset(blk.data(), 0, nblk * sizeof(GwOccBlock));
         uint32_t cnt[4] = {0, 0, 0, 0};
         const uint8_t* bw = h.bwt[s].data();
-        for (size_t b = 0; b < nblk; ++b) {
-            GwOccBlock& o = blk[b];
-            for (int q = 0; q < 4; ++q) o.q[q].x = cnt[q];
-            const uint64_t base = (uint64_t)b * 128;
-            const unsigned lim = (unsigned)std::min<uint64_t>(128, h.N > base ? h.N - base : 0);
-            for (unsigned j = 0; j < lim; ++j) {
-                const unsigned c = bw[base + j];
-                GwU4& qd = o.q[j >> 5];
-                const uint32_t bit = 1u << (j & 31);
-                if (c >= 4) qd.w |= bit;
-                else {
-                    if (c & 1) qd.y |= bit;
-                    if (c & 2) qd.z |= bit;
-                    ++cnt[c];
+        // pieces of blocks are laid out side by side with counts relative to the start of the piece; the counts before each piece
+        // are added in a second sweep
+        const unsigned parts = gw_host_threads();
+        std::vector<uint32_t> piece_cnt((size_t)parts * 4, 0);
+        GwOccBlock* blocks = blk.data();
+        const uint64_t N = h.N;
+        gw_parallel_for(nblk, parts, [&](uint64_t b0, uint64_t b1, unsigned t) {
+            uint32_t c4[4] = {0, 0, 0, 0};
+            for (size_t b = (size_t)b0; b < (size_t)b1; ++b) {
+                GwOccBlock& o = blocks[b];
+                for (int q = 0; q < 4; ++q) o.q[q].x = c4[q];
+                const uint64_t base = (uint64_t)b * 128;
+                const unsigned lim = (unsigned)std::min<uint64_t>(128, N > base ? N - base : 0);
+                for (unsigned j = 0; j < lim; ++j) {
+                    const unsigned c = bw[base + j];
+                    GwU4& qd = o.q[j >> 5];
+                    const uint32_t bit = 1u << (j & 31);
+                    if (c >= 4) qd.w |= bit;
+                    else {
+                        if (c & 1) qd.y |= bit;
+                        if (c & 2) qd.z |= bit;
+                        ++c4[c];
+                    }
                 }
             }
-        }
+            for (int q = 0; q < 4; ++q) piece_cnt[(size_t)t * 4 + q] = c4[q];
+        });
+        std::vector<uint32_t> before((size_t)parts * 4, 0);
+        for (unsigned t = 0; t < parts; ++t)
+            for (int q = 0; q < 4; ++q) { before[(size_t)t * 4 + q] = cnt[q]; cnt[q] += piece_cnt[(size_t)t * 4 + q]; }
+        gw_parallel_for(nblk, parts, [&](uint64_t b0, uint64_t b1, unsigned t) {
+            for (size_t b = (size_t)b0; b < (size_t)b1; ++b)
+                for (int q = 0; q < 4; ++q) blocks[b].q[q].x += before[(size_t)t * 4 + q];
+        });
         uint32_t sum = 0;
         for (int c = 0; c < 4; ++c) { v.C[s][c] = sum; sum += cnt[c]; }
         v.C[s][4] = sum;
@@ -62,14 +79,23 @@ inline void gw_layout_index(const GwHostIndex& h, GwIndexImage& img) {
     v.n_ssa = (uint32_t)h.ssa[0].size();
     const size_t nw = (size_t)(h.N / 64) + 1;
     img.ref_lo.assign(nw, 0); img.ref_hi.assign(nw, 0); img.ref_nf.assign(nw, 0);
-    for (uint64_t i = 0; i < h.N; ++i) {
-        const unsigned c = h.text[(size_t)i];
-        const u64 bit = 1ULL << (i & 63);
-        if (c >= 4) img.ref_nf[(size_t)(i >> 6)] |= bit;
-        else {
-            if (c & 1) img.ref_lo[(size_t)(i >> 6)] |= bit;
-            if (c & 2) img.ref_hi[(size_t)(i >> 6)] |= bit;
-        }
+    {
+        const uint8_t* text = h.text.data();
+        u64 *rl = img.ref_lo.data(), *rh = img.ref_hi.data(), *rn = img.ref_nf.data();
+        const uint64_t N = h.N;
+        gw_parallel_for(nw, gw_host_threads(), [&](uint64_t w0, uint64_t w1, unsigned) {   // whole words per piece: no shared word
+            for (uint64_t w = w0; w < w1; ++w) {
+                const uint64_t lo = w * 64, hi = std::min<uint64_t>(N, lo + 64);
+                u64 l = 0, hh = 0, nf = 0;
+                for (uint64_t i = lo; i < hi; ++i) {
+                    const unsigned c = text[(size_t)i];
+                    const u64 bit = 1ULL << (i & 63);
+                    if (c >= 4) nf |= bit;
+                    else { if (c & 1) l |= bit; if (c & 2) hh |= bit; }
+                }
+                rl[w] = l; rh[w] = hh; rn[w] = nf;
+            }
+        });
     }
     // SequenceBoundary.translate: TreeMap offset -> name, later put wins
     std::map<int64_t, int> by_off;
