@@ -34,7 +34,11 @@ struct Batch {
     std::string names, bases, quals;
     std::vector<uint64_t> name_off{0}, base_off{0}, qual_off{0};
     bool has_qual = true;       // FASTA reads and -q carry no quality (qual == null -> "*")
-    std::string sam;            // SAM text of the batch (filled by a worker)
+    std::vector<gw_hit_t> hits; // hit records and cigar elements of the batch (filled by the align stage of a worker)
+    std::vector<uint32_t> cig;
+    uint64_t nh = 0, nc = 0;
+    bool aligned = false;
+    std::string sam;            // SAM text of the batch (filled by the format stage of a worker)
     int64_t abort_read = -1;    // first read on which the reference throws (its run stops there), -1: none
     gw_counters_t counters{};
     void add(const std::string& name, const std::string& seq_, const std::string* qual) {
@@ -220,49 +224,33 @@ void worker(int device, const Options* o, Channel<BatchPtr>* in, Channel<BatchPt
     const auto t_open = std::chrono::steady_clock::now();
     gw_index_t* ix = nullptr;
     gw_aligner_t* al = nullptr;
-    auto fail = [&](const char* what) { *err = std::string(what) + ": " + gw_last_error(); };
+    std::mutex err_m;   // the align and the format stage may both report
+    auto fail = [&](const char* what) { std::lock_guard<std::mutex> g(err_m); if (err->empty()) *err = std::string(what) + ": " + gw_last_error(); };
+    auto failed = [&] { std::lock_guard<std::mutex> g(err_m); return !err->empty(); };
     if (gw_index_open(o->ref.c_str(), device, &ix) != GW_OK) fail("index");
     else if (gw_aligner_create(ix, &o->cfg, &al) != GW_OK) fail("aligner");
     if (err->empty()) for (auto& t : o->tunables) if (gw_aligner_set_option(al, t.first.c_str(), t.second) != GW_OK) { fail("option"); break; }
     *open_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_open).count();
-    std::vector<gw_hit_t> hits;
-    std::vector<uint32_t> cig, lines;
-    BatchPtr b;
-    // a failed worker still drains its share so the pipeline ends
-    while (in->pop(b)) {
-        if (err->empty() && b->seq == 0 && b->n == 0) {   // start token: SAMOutput.init, "@SQ" lines from this worker's index
-            uint64_t n = 0;
-            gw_sam_header(ix, nullptr, &n);
-            b->sam.resize(n);
-            if (n && gw_sam_header(ix, &b->sam[0], &n) != GW_OK) fail("header");
-        }
-        if (err->empty() && b->n) {
-            const auto t0 = std::chrono::steady_clock::now();
-            hits.resize(std::max<size_t>(hits.size(), (size_t)b->n * 2 + 16));
-            cig.resize(std::max<size_t>(cig.size(), (size_t)b->n * 8 + 64));
-            uint64_t nh = 0, nc = 0;
-            int rc;
-            for (;;) {
-                nh = hits.size(); nc = cig.size();
-                rc = gw_align_batch(al, b->bases.data(), b->base_off.data(), b->n, hits.data(), &nh, cig.data(), &nc, &b->counters);
-                if (rc != GW_E_CAPACITY) break;
-                hits.resize(nh + 16); cig.resize(nc + 64);
-            }
-            if (rc != GW_OK) fail("align");
-            else {
-                for (uint64_t i = 0; i < nh; ++i)   // Align.java has no recovery: the first read the reference throws on ends its run
-                    if (hits[i].is_head && hits[i].status == GW_READ_REF_ABORT) { b->abort_read = hits[i].read_index; break; }
+    // two stages per GPU, so that the device aligns the next batch while the host threads format the previous one:
+    // align (this thread) -> format (SAM text, gw_sam_format uses the host threads) -> writer
+    Channel<BatchPtr> mid(2);
+    std::thread formatter([&] {
+        std::vector<uint32_t> lines;
+        BatchPtr b;
+        while (mid.pop(b)) {
+            if (b->aligned) {
                 lines.assign(b->n, 0);
                 uint64_t len = b->bases.size() * 3 + b->names.size() * 2 + (size_t)b->n * 96 + 64;
+                int rc;
                 for (;;) {
                     b->sam.resize(len);
                     rc = gw_sam_format(ix, b->names.data(), b->name_off.data(), b->bases.data(), b->base_off.data(),
-                                       b->has_qual ? b->quals.data() : nullptr, b->has_qual ? b->qual_off.data() : nullptr, b->n, hits.data(), nh,
-                                       cig.data(), &b->sam[0], &len, lines.data());
+                                       b->has_qual ? b->quals.data() : nullptr, b->has_qual ? b->qual_off.data() : nullptr, b->n, b->hits.data(), b->nh,
+                                       b->cig.data(), &b->sam[0], &len, lines.data());
                     if (rc != GW_E_CAPACITY) break;
                     len += 64;
                 }
-                if (rc != GW_OK) fail("sam");
+                if (rc != GW_OK) { b->sam.clear(); fail("sam"); }
                 else {
                     b->sam.resize(len);
                     if (b->abort_read >= 0 && !o->keep_going) {   // keep the lines of the reads before the aborting one
@@ -273,11 +261,44 @@ void worker(int device, const Options* o, Channel<BatchPtr>* in, Channel<BatchPt
                         b->sam.resize(p);
                     }
                 }
+                std::vector<gw_hit_t>().swap(b->hits);
+                std::vector<uint32_t>().swap(b->cig);
+            }
+            out->push(std::move(b));
+        }
+    });
+    BatchPtr b;
+    // a failed worker still drains its share so the pipeline ends
+    while (in->pop(b)) {
+        if (!failed() && b->seq == 0 && b->n == 0) {   // start token: SAMOutput.init, "@SQ" lines from this worker's index
+            uint64_t n = 0;
+            gw_sam_header(ix, nullptr, &n);
+            b->sam.resize(n);
+            if (n && gw_sam_header(ix, &b->sam[0], &n) != GW_OK) fail("header");
+        }
+        if (!failed() && b->n) {
+            const auto t0 = std::chrono::steady_clock::now();
+            b->hits.resize((size_t)b->n * 2 + 16);
+            b->cig.resize((size_t)b->n * 8 + 64);
+            int rc;
+            for (;;) {
+                b->nh = b->hits.size(); b->nc = b->cig.size();
+                rc = gw_align_batch(al, b->bases.data(), b->base_off.data(), b->n, b->hits.data(), &b->nh, b->cig.data(), &b->nc, &b->counters);
+                if (rc != GW_E_CAPACITY) break;
+                b->hits.resize(b->nh + 16); b->cig.resize(b->nc + 64);
+            }
+            if (rc != GW_OK) fail("align");
+            else {
+                for (uint64_t i = 0; i < b->nh; ++i)   // Align.java has no recovery: the first read the reference throws on ends its run
+                    if (b->hits[i].is_head && b->hits[i].status == GW_READ_REF_ABORT) { b->abort_read = b->hits[i].read_index; break; }
+                b->aligned = true;
             }
             *busy_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         }
-        out->push(std::move(b));
+        mid.push(std::move(b));
     }
+    mid.close();
+    formatter.join();
     if (al) gw_aligner_destroy(al);
     if (ix) gw_index_close(ix);
 }

@@ -174,8 +174,9 @@ GW_HD bool gw_wants_promotion(const GwSlab& s) {
 GW_COLD u64* gw_promote_take(const GwSlab& s) {
     GwReadCtx* c = s.ctx();
     GwExtPool* pool = c->ext_pool;
+    if (pool->block_words <= s.sp.slab_words) { c->ext_pool = nullptr; return nullptr; }   // already in a work area of that size
     const uint32_t idx = gw_atomic_add(&pool->next, 1u);
-    if (idx >= pool->n_blocks || pool->block_words <= s.sp.slab_words) { c->ext_pool = nullptr; return nullptr; }
+    if (idx >= pool->n_blocks) { c->ext_pool = nullptr; return nullptr; }
     return pool->base + (size_t)idx * pool->block_words;
 }
 // ... copy the used part of the work area [0, top) (top is even: the arena starts at an even word, nodes are multiples of two
