@@ -40,15 +40,17 @@ GW_HD void gw_dp_begin(GwDp& d, int m, int Ncols, int band_k, GwU64x2* hist, siz
 }
 
 // peq: [4][GW_MAX_NB] pattern masks of the query (bits >= m clear); refsym(j): reference symbol (0..4) of window column j
-template <typename RefSym>
-GW_HD void gw_dp_columns(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, GwU64x2* hist, size_t stride) {
+// NB: compile-time bound of the number of 64-row blocks (ceil(m / 64) <= NB): the loops over blocks are unrolled to NB, so a 100 bp
+// read does not pay for the two blocks only 250 bp reads have
+template <int NB, typename RefSym>
+GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, GwU64x2* hist, size_t stride) {
     const int w = 64;
     const int m = d.m, bMax = d.bmax;
     int bCeil = d.bceil;
-    int D[GW_MAX_NB];
-    u64 vp[GW_MAX_NB], vn[GW_MAX_NB];
+    int D[NB];
+    u64 vp[NB], vn[NB];
 #pragma unroll
-    for (int r = 0; r < GW_MAX_NB; ++r) { D[r] = d.D[r]; vp[r] = d.vp[r]; vn[r] = d.vn[r]; }
+    for (int r = 0; r < NB; ++r) { D[r] = d.D[r]; vp[r] = d.vp[r]; vn[r] = d.vn[r]; }
     bool hasBest = d.has_best != 0;
     int bestTail = d.best_tail, bestDiff = d.best_diff;
     if (jEnd > d.ncols) jEnd = d.ncols;
@@ -58,7 +60,7 @@ GW_HD void gw_dp_columns(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_
         GwU64x2* col = hist + (size_t)(j + 1) * bMax * stride;
         int computed = bCeil;  // blocks whose column j+1 is written in this step
 #pragma unroll
-        for (int r = 0; r < GW_MAX_NB; ++r) {
+        for (int r = 0; r < NB; ++r) {
             if (r < bCeil) {
                 u64 x = ch < 4 ? peq[ch][r] : 0ULL;
                 if (carry < 0) x |= 1ULL;
@@ -79,7 +81,7 @@ GW_HD void gw_dp_columns(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_
         // activation of the next block (:425-431) — written without dynamic indexing so that D/vp/vn stay in registers
         bool activated = false;
 #pragma unroll
-        for (int r = 1; r < GW_MAX_NB; ++r) {
+        for (int r = 1; r < NB; ++r) {
             if (!activated && r == bCeil && r < bMax) {
                 u64 x = ch < 4 ? peq[ch][r] : 0ULL;
                 if (D[r - 1] - carry <= gw_score_boundary(m, band_k, r - 1) && (((x & 1ULL) != 0ULL) | (carry < 0))) {
@@ -106,25 +108,32 @@ GW_HD void gw_dp_columns(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_
         }
         if (!activated) {   // while (bCeil > 1 && D[bCeil - 1] > scoreBoundary[bCeil - 1] + w) --bCeil;  (:439-441)
 #pragma unroll
-            for (int r = GW_MAX_NB - 1; r >= 1; --r)
+            for (int r = NB - 1; r >= 1; --r)
                 if (bCeil == r + 1 && D[r] > gw_score_boundary(m, band_k, r) + w) bCeil = r;
         }
         // blocks not computed in this step: column j+1 keeps the zero initial value of the Java arrays
         // (a block deactivated just now was computed and keeps its values, as in the reference)
 #pragma unroll
-        for (int r = 1; r < GW_MAX_NB; ++r)
+        for (int r = 1; r < NB; ++r)
             if (r >= computed && r < bMax) col[(size_t)r * stride] = GwU64x2{0ULL, 0ULL};
         if (bCeil == bMax) {
             int dl = D[0];
 #pragma unroll
-            for (int r = 1; r < GW_MAX_NB; ++r) if (r == bMax - 1) dl = D[r];
+            for (int r = 1; r < NB; ++r) if (r == bMax - 1) dl = D[r];
             if (!hasBest) { hasBest = true; bestTail = j; bestDiff = dl; }
             else if (bestDiff > dl) { bestTail = j; bestDiff = dl; }
         }
     }
 #pragma unroll
-    for (int r = 0; r < GW_MAX_NB; ++r) { d.D[r] = D[r]; d.vp[r] = vp[r]; d.vn[r] = vn[r]; }
+    for (int r = 0; r < NB; ++r) { d.D[r] = D[r]; d.vp[r] = vp[r]; d.vn[r] = vn[r]; }
     d.j = jEnd; d.bceil = bCeil; d.has_best = hasBest ? 1 : 0; d.best_tail = bestTail; d.best_diff = bestDiff;
+}
+
+template <typename RefSym>
+GW_HD void gw_dp_columns(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, GwU64x2* hist, size_t stride) {
+    if (d.bmax <= 1) gw_dp_columns_nb<1>(d, jEnd, band_k, peq, refsym, hist, stride);
+    else if (d.bmax <= 2) gw_dp_columns_nb<2>(d, jEnd, band_k, peq, refsym, hist, stride);
+    else gw_dp_columns_nb<GW_MAX_NB>(d, jEnd, band_k, peq, refsym, hist, stride);
 }
 
 // qsym(i): query symbol (0..4) of row i
