@@ -28,34 +28,46 @@ GW_HD uint32_t gw_quarter_count1(const GwU4& qd, uint32_t mask, int ch) {
     return (uint32_t)gw_popc32(h & l & ~qd.w & mask);
 }
 
+// the single-thread forms below work on the block as two 64-symbol halves (quarters 0|1 and 2|3 as one 64-bit word per bit plane):
+// two prefix masks and 64-bit popcounts instead of four masks and 32-bit popcounts
+struct GwHalves { u64 lo[2], hi[2], nf[2]; };
+GW_HD GwHalves gw_halves(const GwBlk& b) {
+    GwHalves h;
+    h.lo[0] = (u64)b.q[0].y | ((u64)b.q[1].y << 32); h.lo[1] = (u64)b.q[2].y | ((u64)b.q[3].y << 32);
+    h.hi[0] = (u64)b.q[0].z | ((u64)b.q[1].z << 32); h.hi[1] = (u64)b.q[2].z | ((u64)b.q[3].z << 32);
+    h.nf[0] = (u64)b.q[0].w | ((u64)b.q[1].w << 32); h.nf[1] = (u64)b.q[2].w | ((u64)b.q[3].w << 32);
+    return h;
+}
+// masks of the symbols of the two halves that lie in the block prefix [0, r), r in 0..127
+GW_HD u64 gw_half_mask0(uint32_t r) { return r >= 64u ? ~0ULL : ((1ULL << r) - 1ULL); }
+GW_HD u64 gw_half_mask1(uint32_t r) { return r <= 64u ? 0ULL : ((1ULL << (r - 64u)) - 1ULL); }
+
 // occurrences of A,C,G,T (N-flagged symbols excluded) in BWT[0, i)  == getOccACGTN without the N column
 GW_HD void gw_rank4(const GwBlk& b, uint32_t r, uint32_t out[4]) {
-    uint32_t a = 0, c = 0, g = 0, t = 0;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const uint32_t lo = b.q[q].y, hi = b.q[q].z;
-        const uint32_t v = ~b.q[q].w & gw_quarter_mask(r, q);
-        const uint32_t tt = (uint32_t)gw_popc32(hi & lo & v), gg = (uint32_t)gw_popc32(hi & ~lo & v), cc = (uint32_t)gw_popc32(~hi & lo & v);
-        t += tt; g += gg; c += cc; a += (uint32_t)gw_popc32(v) - tt - gg - cc;
-    }
+    const GwHalves h = gw_halves(b);
+    const u64 v0 = ~h.nf[0] & gw_half_mask0(r), v1 = ~h.nf[1] & gw_half_mask1(r);
+    const uint32_t t = (uint32_t)(gw_popc64(h.hi[0] & h.lo[0] & v0) + gw_popc64(h.hi[1] & h.lo[1] & v1));
+    const uint32_t g = (uint32_t)(gw_popc64(h.hi[0] & ~h.lo[0] & v0) + gw_popc64(h.hi[1] & ~h.lo[1] & v1));
+    const uint32_t c = (uint32_t)(gw_popc64(~h.hi[0] & h.lo[0] & v0) + gw_popc64(~h.hi[1] & h.lo[1] & v1));
+    const uint32_t a = (uint32_t)(gw_popc64(v0) + gw_popc64(v1)) - t - g - c;
     out[0] = b.q[0].x + a; out[1] = b.q[1].x + c; out[2] = b.q[2].x + g; out[3] = b.q[3].x + t;
 }
 
 // occurrences of one symbol ch (0..3) in BWT[0, i)
 GW_HD uint32_t gw_rank1(const GwBlk& b, uint32_t r, int ch) {
-    uint32_t n = 0;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) n += gw_quarter_count1(b.q[q], gw_quarter_mask(r, q), ch);
+    const GwHalves h = gw_halves(b);
+    const u64 h0 = (ch & 2) ? h.hi[0] : ~h.hi[0], h1 = (ch & 2) ? h.hi[1] : ~h.hi[1];
+    const u64 l0 = (ch & 1) ? h.lo[0] : ~h.lo[0], l1 = (ch & 1) ? h.lo[1] : ~h.lo[1];
+    const uint32_t n = (uint32_t)(gw_popc64(h0 & l0 & ~h.nf[0] & gw_half_mask0(r)) + gw_popc64(h1 & l1 & ~h.nf[1] & gw_half_mask1(r)));
     const uint32_t base = ch == 0 ? b.q[0].x : ch == 1 ? b.q[1].x : ch == 2 ? b.q[2].x : b.q[3].x;
     return base + n;
 }
 
 // number of N in BWT[0, i): block start minus the four counters, plus N flags in the prefix
 GW_HD uint32_t gw_rankN(const GwBlk& b, uint32_t blockStart, uint32_t r) {
-    uint32_t n = blockStart - (b.q[0].x + b.q[1].x + b.q[2].x + b.q[3].x);
-#pragma unroll
-    for (int q = 0; q < 4; ++q) n += (uint32_t)gw_popc32(b.q[q].w & gw_quarter_mask(r, q));
-    return n;
+    const GwHalves h = gw_halves(b);
+    const uint32_t n = blockStart - (b.q[0].x + b.q[1].x + b.q[2].x + b.q[3].x);
+    return n + (uint32_t)(gw_popc64(h.nf[0] & gw_half_mask0(r)) + gw_popc64(h.nf[1] & gw_half_mask1(r)));
 }
 
 GW_HD uint32_t gw_clampN(const GwIndexView& ix, uint32_t i) { return i > ix.N ? ix.N : i; }
