@@ -184,7 +184,7 @@ GW_COLD int gw_fused_trace_tick(const GwSearchEnv& env, const GwSlab& s, uint32_
 }
 
 // DP columns [d.j, jEnd) of a job
-GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int n_cols, GwU64x2* hist, size_t stride) {
+GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int n_cols, GwU64x2* hist, size_t stride, int nb_hint = 0) {
     GwDp d = job->dp;
     int rw = -1; u64 rl = 0, rh = 0, rn = 0;
     auto refsym = [&](int j) -> int {   // columns advance one by one: reload the window words every 64 columns only
@@ -193,7 +193,7 @@ GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int n_cols, GwU64x
         if ((rn >> sft) & 1ULL) return 4;
         return (int)((((rh >> sft) & 1ULL) << 1) | ((rl >> sft) & 1ULL));
     };
-    gw_dp_columns(d, d.j + n_cols, env.cfg.band_width, job->peq, refsym, hist, stride);
+    gw_dp_columns(d, d.j + n_cols, env.cfg.band_width, job->peq, refsym, hist, stride, nb_hint);
     job->dp = d;
 }
 

@@ -430,10 +430,19 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
                 atomicAdd(&c->occ_locate, (uint32_t)j);   // the two fragments of a read are walked by different lanes
             }
             __syncwarp();
-            if (lane < nb && c->phase != GW_PH_WAIT_EXACT) {   // exact hit: no verification (:490-494)
-                GwSlab sv(slabs[id >> 1]);
+            {   // DP + traceback; the lanes take the DP instantiation of the largest block count among them
                 GwJob job;
-                gw_verify_frag(env, sv, &job, (int)(id & 1u), my_hist, stride);
+                GwSlab sv;
+                bool dp = false;
+                if (lane < nb && c->phase != GW_PH_WAIT_EXACT) {   // exact hit: no verification (:490-494)
+                    sv = GwSlab(slabs[id >> 1]);
+                    dp = gw_job_begin_dp(env, sv, &job, (int)(id & 1u), my_hist, stride);
+                }
+                const int hint = (int)__reduce_max_sync(FULL, dp ? (unsigned)job.dp.bmax : 0u);
+                if (dp) {
+                    gw_job_columns(env, &job, job.dp.ncols, my_hist, stride, hint);
+                    gw_job_trace(sv, &job, my_hist, stride);
+                }
             }
             __syncwarp();
             const uint32_t nid = __shfl_down_sync(FULL, id, 1);
