@@ -116,6 +116,50 @@ def oracle_baseline(args, fa, reads_arr, n_sample, threads):
     return len(reads) / res["elapsed"], res
 
 
+def parity_check(lib, L, idx, bsf, reads_arr, h_hits, n_hits, h_cig, oracle_res, n_s):
+    """the timed GPU batch against the oracle on the first n_s reads of the same workload: whole SAM lines and the four per-read
+    debug counters (reads on which the reference throws: status only). Returns the `parity` object of the JSON line."""
+    hits = h_hits.numpy().view(L.HIT_DTYPE)[:n_hits]
+    cut = int(np.searchsorted(hits["read_index"], n_s, side="left"))
+    sub = np.ascontiguousarray(hits[:cut])
+    m = reads_arr.shape[1]
+    names = ["r%d" % i for i in range(n_s)]
+    nb, noff = L.concat(names)
+    bases = np.ascontiguousarray(reads_arr[:n_s]).reshape(-1)
+    boff = np.arange(n_s + 1, dtype=np.uint64) * np.uint64(m)
+    lines = np.zeros(max(n_s, 1), dtype=np.uint32)
+    cap = C.c_uint64(n_s * (2 * m + 200) + 4096)
+    buf = C.create_string_buffer(int(cap.value))
+    cig = h_cig.numpy().view(np.uint32)
+    L.check(lib.gw_sam_format(idx._h, L.ptr(nb), L.ptr(noff), L.ptr(bases), L.ptr(boff), None, None, n_s, L.ptr(sub), len(sub), L.ptr(cig),
+                              C.cast(buf, C.c_void_p), C.byref(cap), L.ptr(lines)))
+    got_lines = buf.raw[:cap.value].decode().split("\n")[:-1]
+    ctr = np.zeros((n_s, 4), dtype=np.uint32)
+    L.check(lib.gw_aligner_read_counters(bsf._h, 0, n_s, L.ptr(ctr)))
+    status = np.full(n_s, -1, dtype=np.int32)
+    heads = sub[sub["is_head"] == 1]
+    status[heads["read_index"][::-1]] = heads["status"][::-1]
+    mism, cmism, first, p = 0, 0, None, 0
+    for i in range(n_s):
+        g = got_lines[p:p + int(lines[i])]
+        p += int(lines[i])
+        w = oracle_res["sam"][i]
+        ws = oracle_res["status"][i]
+        bad = g != w or int(status[i]) != ws
+        badc = ws != 2 and [int(x) for x in ctr[i]] != list(oracle_res["counters"][i])
+        if bad:
+            mism += 1
+        if badc:
+            cmism += 1
+        if (bad or badc) and first is None:
+            first = {"read": i, "got": g, "want": w, "got_counters": [int(x) for x in ctr[i]], "want_counters": list(oracle_res["counters"][i])}
+    out = {"checked": n_s, "mismatches": mism, "counter_mismatches": cmism,
+           "what": "whole SAM lines + status + numFMIndexSearches/numSW/numCutOff/numFiltered per read, GPU (timed e2e batch) vs C++ oracle"}
+    if first:
+        out["first_mismatch"] = first
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -139,7 +183,8 @@ def run_reference(args):
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1000.0 * sum(times) / len(times), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64",
-        "data": "synthetic", "config": dict(workload="configs[1]: 100 Mbp synthetic genome, 100 bp reads, k=3 (CPU oracle; the JVM reference cannot run here)", **workload(args)),
+        "data": "synthetic", "config": dict(workload="configs[1]: 100 Mbp synthetic genome, 100 bp reads, k=3 (CPU oracle; the JVM reference cannot run here)",
+                                                      **dict(workload(args), reads_per_step=n_sample, reads_in_workload=args.reads)),
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample_desc},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "index_built_by": how}))
 
@@ -295,15 +340,24 @@ def run_ours(args):
             "gpu_launches": int(counters["gpu_launches"]) * args.steps, "counters_per_step": counters,
             "clocks": sampler.summary(),
         }
-        if world == 1 and not args.no_cpu:
+        parity_bad = False
+        if not args.no_cpu:
             threads = os.cpu_count() or 1
-            n_s = min(n, args.ref_sample)
+            n_s = min(n, args.ref_sample if world == 1 else min(args.ref_sample, 20_000))
             v, res = oracle_baseline(args, fa, reads, n_s, threads)
-            v1, _ = oracle_baseline(args, fa, reads, max(1, n_s // max(threads, 1)), 1)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": "first %d reads of the workload, %d threads sharing one index (C++ oracle; JVM reference unavailable on this box)" % (n_s, threads),
-                                    "single_thread_value": v1}
+            if world == 1:
+                v1, _ = oracle_baseline(args, fa, reads, max(1, n_s // max(threads, 1)), 1)
+                line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                        "sample": "first %d reads of the workload, %d threads sharing one index (C++ oracle; JVM reference unavailable on this box)" % (n_s, threads),
+                                        "single_thread_value": v1}
+            line["parity"] = parity_check(lib, L, idx, bsf, reads, h_hits, e_nh, h_cig, res, n_s)
+            parity_bad = line["parity"]["mismatches"] != 0 or line["parity"]["counter_mismatches"] != 0
         print(json.dumps(line))
+        if parity_bad:
+            sys.stderr.write("bench.py: the GPU output differs from the oracle on the checked sample\n")
+            bsf.close()
+            idx.close()
+            sys.exit(3)
     bsf.close()
     idx.close()
     if world > 1:

@@ -54,6 +54,7 @@ SYMBOLS = {
     "gw_align_batch": (C.c_int, [_P, _P, _P, C.c_uint32, _P, C.POINTER(C.c_uint64), _P, C.POINTER(C.c_uint64), C.POINTER(Counters)]),
     "gw_align_batch_device": (C.c_int, [_P, _P, _P, C.c_uint32, C.c_uint64, C.c_uint32, _P, C.c_uint64, _P, C.c_uint64, C.POINTER(C.c_uint64),
                                         C.POINTER(C.c_uint64), C.POINTER(Counters)]),
+    "gw_aligner_read_counters": (C.c_int, [_P, C.c_uint32, C.c_uint32, _P]),
     "gw_aligner_last_timing": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "gw_sam_format": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, C.c_uint32, _P, C.c_uint64, _P, _P, C.POINTER(C.c_uint64), _P]),
     "gw_sam_header": (C.c_int, [_P, _P, C.POINTER(C.c_uint64)]),

@@ -111,8 +111,10 @@ class FMIndexOnGenome:
 class AlignmentBatch:
     """hit records of one batch (gw_hit_t array + BAM-encoded cigar elements), convertible to SAM text"""
 
-    def __init__(self, index, seqs_bytes, seq_off, hits, cigars, counters, timing):
+    def __init__(self, index, seqs_bytes, seq_off, hits, cigars, counters, timing, read_counters=None):
         self.index, self.bases, self.base_off, self.hits, self.cigars, self.counters, self.timing = index, seqs_bytes, seq_off, hits, cigars, counters, timing
+        # (n, 4) uint32: numFMIndexSearches, numSW, numCutOff, numFiltered of every read (BidirectionalSuffixFilter.java:588-592)
+        self.read_counters = read_counters
 
     def sam(self, names, quals=None):
         """SAMOutput.emit of every record, in input order; returns (text, lines_per_read)"""
@@ -184,7 +186,9 @@ class BidirectionalSuffixFilter:
             break
         ms = (C.c_float * 6)()
         L.lib().gw_aligner_last_timing(self._h, ms)
-        return AlignmentBatch(self.fmIndex, b, off, hits[:nh.value].copy(), cig[:max(int(nc.value), 1)].copy(), cnt.as_dict(), list(ms))
+        rc4 = np.zeros((max(n, 1), 4), dtype=np.uint32)
+        L.check(L.lib().gw_aligner_read_counters(self._h, 0, n, L.ptr(rc4)))
+        return AlignmentBatch(self.fmIndex, b, off, hits[:nh.value].copy(), cig[:max(int(nc.value), 1)].copy(), cnt.as_dict(), list(ms), rc4[:n])
 
     def close(self):
         if self._h:

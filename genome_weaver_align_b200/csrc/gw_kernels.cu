@@ -576,7 +576,8 @@ __global__ void gw_settle_kernel(u64** slabs, u64* small_base, size_t small_word
     gw_settle(slabs[slot], sm, small_sp, cfg);
     slabs[slot] = sm;
 }
-__global__ void gw_emit_count_kernel(u64* const* slabs, uint32_t n, GwDevConfig cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals) {
+__global__ void gw_emit_count_kernel(u64* const* slabs, uint32_t n, GwDevConfig cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals,
+                                     uint32_t* read_ctr) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long v[7] = {0, 0, 0, 0, 0, 0, 0};
     if (i < n) {
@@ -584,6 +585,8 @@ __global__ void gw_emit_count_kernel(u64* const* slabs, uint32_t n, GwDevConfig 
         const GwReadCtx* c = reinterpret_cast<const GwReadCtx*>(slabs[i]);
         v[0] = (unsigned long long)c->n_fm; v[1] = (unsigned long long)c->n_sw; v[2] = (unsigned long long)c->n_cut; v[3] = (unsigned long long)c->n_filt;
         v[4] = c->occ_scan; v[5] = 2u * (uint32_t)c->n_fm; v[6] = c->occ_locate;
+        // the reference's per-read debug counters (BidirectionalSuffixFilter.java:588-592), kept for gw_aligner_read_counters
+        if (read_ctr) reinterpret_cast<uint4*>(read_ctr)[i] = make_uint4((uint32_t)c->n_fm, (uint32_t)c->n_sw, (uint32_t)c->n_cut, (uint32_t)c->n_filt);
     }
 #pragma unroll
     for (int j = 0; j < 7; ++j) {
@@ -798,8 +801,9 @@ void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32
 void gwk_settle(cudaStream_t st, u64** slabs, u64* small_base, size_t small_words, const GwSlabParams& small_sp, const uint32_t* list, uint32_t n, const GwDevConfig& cfg) {
     if (n) gw_settle_kernel<<<gw_grid(n, 128), 128, 0, st>>>(slabs, small_base, small_words, small_sp, list, n, cfg);
 }
-void gwk_emit_count(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals) {
-    if (n) gw_emit_count_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, cfg, n_rec, n_cig, totals);
+void gwk_emit_count(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals,
+                    uint32_t* read_ctr) {
+    if (n) gw_emit_count_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, cfg, n_rec, n_cig, totals, read_ctr);
 }
 void gwk_scan2(cudaStream_t st, const uint32_t* a, const uint32_t* b, uint32_t n, unsigned long long base_a, unsigned long long base_b,
                unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot, unsigned long long* part) {

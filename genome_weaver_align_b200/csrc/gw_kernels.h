@@ -19,7 +19,8 @@ void gwk_locate(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const
 void gwk_verify(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n, int band_k, void* hist);
 void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count);
 void gwk_settle(cudaStream_t st, u64** slabs, u64* small_base, size_t small_words, const GwSlabParams& small_sp, const uint32_t* list, uint32_t n, const GwDevConfig& cfg);
-void gwk_emit_count(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals);
+void gwk_emit_count(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals,
+                    uint32_t* read_ctr /* 4 x n: fm searches, sw calls, cut-offs, filtered; may be null */);
 void gwk_scan2(cudaStream_t st, const uint32_t* a, const uint32_t* b, uint32_t n, unsigned long long base_a, unsigned long long base_b,
                unsigned long long* oa, unsigned long long* ob, unsigned long long* out_tot, unsigned long long* part /* 2048 words of scratch */);
 void gwk_emit_write(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t read_base, const unsigned long long* rec_off,

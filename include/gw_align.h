@@ -125,6 +125,10 @@ int gw_align_batch_device(gw_aligner_t*, const char* d_bases, const uint64_t* d_
  * aligner's stream: [0] prep+quick-scan, [1] search, [2] locate, [3] verify, [4] finalize, [5] whole batch */
 int gw_aligner_last_timing(const gw_aligner_t*, float ms[6]);
 
+/* the reference's per-read debug counters (align/strategy/BidirectionalSuffixFilter.java:224-233, :588-592) of reads
+ * [first, first+n) of the last gw_align_batch* call: out[4*i..] = numFMIndexSearches, numSW, numCutOff, numFiltered */
+int gw_aligner_read_counters(const gw_aligner_t*, uint32_t first, uint32_t n, uint32_t* out);
+
 /* tunables of an aligner (all optional): "scan_coop" 0/1 (4-lane cooperative quick scan, default 1), "slab_words" (8-byte words of the
  * per-read work area of the first pass), "big_slab_words" (second pass), "wave_reads" (reads resident per wave) */
 int gw_aligner_set_option(gw_aligner_t*, const char* name, int64_t value);
