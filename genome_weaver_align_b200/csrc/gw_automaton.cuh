@@ -1,26 +1,23 @@
 // gw_automaton.cuh — resumable per-read driver around gw_search.cuh: AlignmentProcess.align_internal
 // (reference: align/src/main/java/org/utgenome/weaver/align/strategy/BidirectionalSuffixFilter.java:278-477) cut at the
 // points where the reference calls into the sampled suffix array and the verifier (verify :496-560). At those points the
-// read parks with up to two fragment requests; the locate and verify kernels fill them and the read resumes.
+// read parks with up to two fragment requests; the verification batch of the flow kernel fills them and the read resumes.
+//
+// Two kinds of code live here. The HOT slices (gw_lane_poll, gw_lane_try) run on the lane's register copy of the read
+// (GwLane, gw_search.cuh) and are written to stay small and branch-poor: they are the loop every search step goes through.
+// The COLD continuations (taking a read up, reporting a chain, split / soft-clip children) are out-of-line functions that work on
+// the read's work area in HBM; the caller writes the lane back before and re-reads it after them.
 #pragma once
 #include "gw_search.cuh"
 
-struct GwRoundQueues {
-    uint32_t* next_active;   // slots that parked in this round
-    uint32_t* locate_req;    // slot*2 + fragment
-    uint32_t* verify_req;    // slot*2 + fragment
-    uint32_t* counters;      // [0] n_next_active, [1] n_locate, [2] n_verify
-};
-
 GW_HD void gw_fail(GwReadCtx* c, int status) { c->status = status; c->phase = GW_PH_DONE; }
 
-GW_HD int gw_q_symbol(const GwReadCtx* c, int strand, int i) {
-    return (int)((((c->qhi[strand][i >> 6] >> (i & 63)) & 1ULL) << 1) | ((c->qlo[strand][i >> 6] >> (i & 63)) & 1ULL));
-}
+#define GW_STEP_CONTINUE 0
+#define GW_STEP_PARKED 1
+#define GW_STEP_DONE 2
 
 // reportAlignment request side: classify the fragments of the chain headed by `base`; returns true if the read must park
-GW_COLD bool gw_begin_report(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, int32_t base,
-                                                const GwRoundQueues& rq) {
+GW_COLD bool gw_begin_report(const GwSearchEnv& env, const GwSlab& s, int32_t base) {
     GwReadCtx* c = s.ctx();
     c->pend_base = base;
     int n = 0;
@@ -37,11 +34,6 @@ GW_COLD bool gw_begin_report(const GwSearchEnv& env, const GwSlab& s, uint32_t s
             pf->sa_index = st->cur_lb;
             // FMIndexOnGenome.toCoordinate: fm = ~(strand ^ (dir.isForward ? 0 : 1)) & 1
             pf->fm = ~(gw_strand(st) ^ (gw_is_fwd(st) ? 0 : 1)) & 1;
-            if (rq.counters) {   // round mode; the fused kernel serves the request on the same lane (gw_fused.cuh)
-                uint32_t id = slot * 2u + (uint32_t)n;
-                rq.locate_req[gw_atomic_add(&rq.counters[1], 1u)] = id;
-                rq.verify_req[gw_atomic_add(&rq.counters[2], 1u)] = id;
-            }
             need = true;
         }
     }
@@ -105,34 +97,10 @@ GW_COLD void gw_finish_report(const GwSearchEnv& env, const GwSlab& s) {
     if (!gw_add_result(s, env.cfg, first)) gw_fail(c, GW_ST_OVERFLOW);
 }
 
-// staircase table of the current minMismatches; returns nullptr and fails the read where the reference constructor throws.
-// The table only changes when minMismatches does (a reported hit), so its offset is kept in the context: the usual call reads
-// three words of the context header instead of walking m -> abort bitmap -> table base.
-GW_HD const u64* gw_staircase_for(const GwSearchEnv& env, GwReadCtx* c, int* kk) {
-    const int mm = c->min_mm;
-    *kk = mm;
-    if (c->sf_mm != mm) {
-        const int m = c->m;
-        int off = -1;
-        if (mm >= 0 && !((env.sf.abort_by_m[m] >> mm) & 1u)) off = env.sf.base_by_m[m] + ((m + 63) >> 6) * (mm * (mm + 1) / 2);
-        c->sf_mm = mm; c->sf_off = off;
-    }
-    const int off = c->sf_off;
-    if (off < 0) { gw_fail(c, GW_ST_ABORT); return nullptr; }
-    return env.sf.words + off;
-}
-
-// ---- resumable driver ------------------------------------------------------------------------------------
-// A read is advanced by gw_resume_read (once, when a thread picks the read up: consumes locate/verify results, seeds the
-// queue) followed by gw_step_read calls, each of which is ONE iteration of the reference's `while (!queue.isEmpty())` loop
-// (:352-475). Splitting the loop body out lets the search kernel keep all lanes of a warp busy: a lane whose read parks or
-// finishes fetches the next read instead of idling until the slowest read of the warp is done.
-#define GW_STEP_CONTINUE 0
-#define GW_STEP_PARKED 1
-#define GW_STEP_DONE 2
-
-// returns GW_STEP_CONTINUE when the read is in the best-first loop and wants gw_step_read calls
-GW_COLD int gw_resume_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
+// ---- taking a read up ------------------------------------------------------------------------------------
+// Consumes what the read was parked for (exact-hit locate, verification results) or seeds the queue from the quick-scan results
+// (:296-349); returns GW_STEP_CONTINUE when the read is in the best-first loop and wants search slices.
+GW_COLD int gw_resume_read(const GwSearchEnv& env, const GwSlab& s) {
     GwReadCtx* c = s.ctx();
     const int m = c->m, k = c->k;
     const GwDevConfig& cfg = env.cfg;
@@ -164,10 +132,6 @@ GW_COLD int gw_resume_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slo
                 c->pend[0].sa_index = c->scan_lb[strand];
                 c->pend[0].fm = strand == 0 ? 1 : 0;  // FMIndexOnGenome.toCoordinate(saIndex, strand)
                 c->pend_n = 1;
-                if (rq.counters) {
-                    rq.locate_req[gw_atomic_add(&rq.counters[1], 1u)] = slot * 2u;
-                    rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
-                }
                 c->phase = GW_PH_WAIT_EXACT;
                 return GW_STEP_PARKED;
             }
@@ -186,92 +150,25 @@ GW_COLD int gw_resume_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slo
     return GW_STEP_CONTINUE;
 }
 
-// parks a running read without a request: it is simply continued in the next round (used to bound the tail of a launch)
-GW_HD void gw_yield_read(const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
-    (void)s;
-    rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
-}
-
-// One iteration of the best-first loop is cut in two kinds of slices so that the lanes of a warp run the expensive part together:
-//   gw_search_poll   poll the queue, hit test / cut-offs (:352-409); leaves the lane "mid step" when there are candidates to try
-//   gw_search_try    ONE candidate extension = one FM step + one NFA step + one queue insertion (:415-455); the candidates of a
-//                    step (the read's own base first, then A,C,G,T) are tried by consecutive calls; after the last one the
-//                    split / soft-clip children are generated (:457-474)
-// Which candidates are done is recorded in the checked-base flags of the state itself (SearchState.state bits 0-4), exactly where
-// the reference keeps them, so a lane only carries the two arena offsets below between slices.
-struct GwSearchLane {
-    int32_t base;    // polled queue entry (head of the split chain)
-    int32_t c_off;   // fragment of the chain that is being extended
-    int32_t mid;     // 1: candidates of the current step remain
-};
-
 // the chain headed by `base` is complete: classify its fragments (park for locate + verification) or report it at once (:366-379)
-GW_COLD int gw_search_report(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq, int32_t base) {
+GW_COLD int gw_search_report(const GwSearchEnv& env, const GwSlab& s, int32_t base) {
     GwReadCtx* c = s.ctx();
-    if (gw_begin_report(env, s, slot, base, rq)) {
+    if (gw_begin_report(env, s, base)) {
         c->phase = GW_PH_WAIT_VERIFY;
-        if (rq.counters) rq.next_active[gw_atomic_add(&rq.counters[0], 1u)] = slot;
         return GW_STEP_PARKED;
     }
     gw_finish_report(env, s);
     return c->phase == GW_PH_DONE ? GW_STEP_DONE : GW_STEP_CONTINUE;
 }
 
-// L.mid after a slice: 0 step finished, GW_MID_TRY candidates remain; with DEFER (warp-pool kernel) the rarely taken, long
-// continuations are not run inside the slice but left as GW_MID_SPLIT / GW_MID_REPORT for the caller, which runs them for
-// several lanes of the warp at once (gw_search_split, gw_search_report)
-#define GW_MID_TRY 1
-#define GW_MID_SPLIT 2
-#define GW_MID_REPORT 3
-
-template <bool DEFER = false>
-GW_HD int gw_search_poll(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq, GwSearchLane& L) {
-    GwReadCtx* c = s.ctx();
-#if defined(__CUDA_ARCH__)
-    // a step touches, one after the other, the context header, the head of the queue, the polled state and the read's bit planes:
-    // the lines whose addresses are known now are requested together, so that their misses overlap
-    asm volatile("prefetch.global.L1 [%0];" ::"l"(s.queue()));
-    asm volatile("prefetch.global.L1 [%0];" ::"l"(&c->qlo[0][0]));
-#endif
-    const int m = c->m;
-    const GwDevConfig& cfg = env.cfg;
-    L.mid = 0;
-    if (c->qn <= 0 || c->n_fm > m * 20) { c->phase = GW_PH_DONE; return GW_STEP_DONE; }   // queue empty / fmIndexSearchUpperBound
-    const int32_t base = gw_queue_poll(s, cfg);
-    int32_t c_off = base;
-    const GwState* C = gw_st(s, base);
-    for (;;) {   // first fragment of the chain that still has bases to process (:366-379)
-        if (!(gw_has_hit(C) || gw_is_clipped(C) || gw_remaining(C) == 0)) break;
-        if (C->next_split < 0) {
-            if (DEFER) { L.base = base; L.mid = GW_MID_REPORT; return GW_STEP_CONTINUE; }
-            return gw_search_report(env, s, slot, rq, base);
-        }
-        c_off = C->next_split;
-        C = gw_st(s, c_off);
-    }
-    if (gw_is_finished(C)) return GW_STEP_CONTINUE;
-    const int nm = gw_lower_k(C);
-    if (nm > c->min_mm) { c->n_cut++; return GW_STEP_CONTINUE; }
-    {
-        const int scoreUB = gw_score(s, cfg, gw_st(s, base), true);
-        if (scoreUB < 0 || scoreUB < c->best_score) { c->n_cut++; return GW_STEP_CONTINUE; }
-    }
-    // the staircase filter of the current minMismatches is needed on every path from here (:425, :439); where the reference's
-    // constructor throws, the read ends here whichever path asked for it
-    int kk;
-    if (!gw_staircase_for(env, c, &kk)) return GW_STEP_DONE;
-    L.base = base; L.c_off = c_off; L.mid = 1;
-    return GW_STEP_CONTINUE;
-}
-
 // split / soft-clip children of the state whose candidates are exhausted (:457-474)
-GW_COLD int gw_search_split(const GwSearchEnv& env, const GwSlab& s, const GwSearchLane& L) {
+GW_COLD int gw_search_split(const GwSearchEnv& env, const GwSlab& s, int32_t base, int32_t c_off) {
     GwReadCtx* c = s.ctx();
     const int m = c->m, k = c->k;
     const GwDevConfig& cfg = env.cfg;
-    const GwState C = gw_load_state(s, L.c_off);
+    const GwState C = gw_load_state(s, c_off);
     const int nm = gw_lower_k(&C);
-    if (gw_num_split(s, gw_st(s, L.base)) < cfg.num_split_allowed && nm + 1 <= c->min_mm) {
+    if (gw_num_split(s, gw_st(s, base)) < cfg.num_split_allowed && nm + 1 <= c->min_mm) {
         const int index = gw_next_index(&C);
         if (index > cfg.indel_end_skip && m - index >= cfg.indel_end_skip) {
 #pragma unroll 1
@@ -279,7 +176,7 @@ GW_COLD int gw_search_split(const GwSearchEnv& env, const GwSlab& s, const GwSea
                 const int32_t ns = gw_split_state(env, s, C, k, clip != 0);
                 if (ns == -2) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
                 if (ns == -3) { gw_fail(c, GW_ST_ABORT); return GW_STEP_DONE; }
-                if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, L.base, L.c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
+                if (ns >= 0) { if (!gw_queue_add(s, cfg, gw_update(s, base, c_off, ns))) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; } }
                 else if (clip == 0) c->n_filt++;
             }
         }
@@ -287,21 +184,112 @@ GW_COLD int gw_search_split(const GwSearchEnv& env, const GwSlab& s, const GwSea
     return GW_STEP_CONTINUE;
 }
 
-template <bool DEFER = false, int MAXH = GW_MAX_ROWS>
-GW_HD int gw_search_try(const GwSearchEnv& env, const GwSlab& s, GwSearchLane& L) {
+// a new state of a split chain enters the queue through the chain's head (SearchState.update :861-875); rare: out of line
+template <int MAXH>
+GW_COLD bool gw_lane_chain_insert(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln, int32_t ns) {
+    gw_lane_flush(s, ln);
+    const bool ok = gw_queue_add(s, env.cfg, gw_update(s, ln.base, ln.c_off, ns));
+    gw_lane_reload(s, ln);
+    return ok;
+}
+
+// ---- hot slices ------------------------------------------------------------------------------------------
+// One iteration of the reference's `while (!queue.isEmpty())` loop (:352-475) is cut in two kinds of slices so that the lanes of
+// a warp run the expensive part together:
+//   gw_lane_poll   poll the queue, hit test / cut-offs (:352-409); leaves the lane "mid step" when there are candidates to try
+//   gw_lane_try    ONE candidate extension = one FM step + one NFA step + one queue insertion (:415-455); the candidates of a
+//                  step (the read's own base first, then A,C,G,T) are tried by consecutive calls; after the last one the
+//                  split / soft-clip children are generated (:457-474)
+// After a slice ln.mid tells what remains of the step: 0 nothing, GW_MID_TRY candidates, GW_MID_SPLIT / GW_MID_REPORT one of the
+// out-of-line continuations (gw_lane_split, gw_lane_report), which the caller runs for several lanes of the warp at once.
+
+GW_HD bool gw_state_complete(const GwState* st) { return gw_has_hit(st) || gw_is_clipped(st) || gw_remaining(st) == 0; }
+
+// staircase table of the current minMismatches (:425, :439); nullptr (and the read fails) where the reference's constructor throws.
+// The table only changes when minMismatches does (a reported hit), so its offset is kept in the lane.
+template <int MAXH>
+GW_HD const u64* gw_lane_staircase(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln) {
+    const int mm = ln.min_mm;
+    if (ln.sf_mm != mm) {
+        const int m = ln.m;
+        int off = -1;
+        if (mm >= 0 && !((env.sf.abort_by_m[m] >> mm) & 1u)) off = env.sf.base_by_m[m] + ((m + 63) >> 6) * (mm * (mm + 1) / 2);
+        ln.sf_mm = mm; ln.sf_off = off;
+    }
+    if (ln.sf_off < 0) { gw_fail(s.ctx(), GW_ST_ABORT); return nullptr; }
+    return env.sf.words + ln.sf_off;
+}
+
+template <int MAXH>
+GW_HD int gw_lane_poll(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln) {
     GwReadCtx* c = s.ctx();
     const GwDevConfig& cfg = env.cfg;
-    GwState* Cp = gw_st(s, L.c_off);
-    const GwState C = *Cp;
+    ln.mid = 0;
+    if (ln.qn <= 0 || ln.n_fm > ln.m * 20) { c->phase = GW_PH_DONE; return GW_STEP_DONE; }   // queue empty / fmIndexSearchUpperBound
+    const int32_t base = gw_lq_poll(s, ln);
+    if (base != ln.cached) gw_lane_fetch(s, ln, base);
+    ln.base = base;
+    int32_t c_off = base;
+    if (gw_state_complete(&ln.C)) {   // first fragment of the chain that still has bases to process (:366-379)
+        int32_t o = ln.C.next_split;
+        for (;;) {
+            if (o < 0) { ln.mid = GW_MID_REPORT; return GW_STEP_CONTINUE; }
+            const GwState* st = gw_st(s, o);
+            if (!gw_state_complete(st)) break;
+            o = st->next_split;
+        }
+        c_off = o;
+        gw_lane_fetch(s, ln, o);
+    }
+    ln.c_off = c_off;
+    const GwState& C = ln.C;
+    const bool exclusive = c_off == base && C.next_split < 0;
+    if (gw_is_finished(&C)) return GW_STEP_CONTINUE;
+    const int nm = gw_lower_k(&C);
+    bool cut = nm > ln.min_mm;
+    if (!cut) {
+        const int scoreUB = exclusive ? (gw_frag_len(&C) - nm) * cfg.match_score - nm * cfg.mismatch_penalty : gw_score(s, cfg, gw_st(s, base), true);
+        cut = scoreUB < 0 || scoreUB < ln.best_score;
+    }
+    if (cut) {
+        ln.n_cut++;
+        if (exclusive) gw_lane_free_state(ln, base);
+        return GW_STEP_CONTINUE;
+    }
+    // the staircase filter of the current minMismatches is needed on every path from here (:425, :439); where the reference's
+    // constructor throws, the read ends here whichever path asked for it
+    if (!gw_lane_staircase(env, s, ln)) return GW_STEP_DONE;
+    ln.mid = GW_MID_TRY;
+    return GW_STEP_CONTINUE;
+}
+
+// ONE candidate extension of the state in the lane's registers: candidate choice (:415-455), Cursor.nextSi +
+// FMIndexOnGenome.bidirectionalSearch (two rank queries on one index, FMIndexOnGenome.java:148-194), ReadAlignmentNFA.nextState +
+// SearchState.nextState (ReadAlignmentNFA.java:146-215), queue insertion. MAXH: compile-time bound of the NFA height (k + 1): for
+// MAXH <= 8 the rows stay in registers (every loop over rows is unrolled with constant indices).
+template <int MAXH>
+GW_HD int gw_lane_try(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln) {
+    GwReadCtx* c = s.ctx();
+    const GwDevConfig& cfg = env.cfg;
+    const GwIndexView& ix = env.ix;
+    GwState& C = ln.C;
+    const bool exclusive = ln.c_off == ln.base && C.next_split < 0;
     const int strand = gw_strand(&C);
-    const int nextBase = gw_q_symbol(c, strand, gw_next_index(&C));
+    const int dir = gw_dir(&C);
+    const bool fwdC = dir != GW_DIR_B;
+    const int nextIdx = fwdC ? C.cursor : C.cursor - 1;
+    const int nextBase = gw_q_symbol(c, strand, nextIdx);
     int flags = C.state;
     // next candidate in the reference's order: the read's own base, then A,C,G,T; checked or empty ones are passed over (and
-    // marked checked) (:415-455). Written without branches so that the lanes of a warp stay together up to the FM step.
+    // marked checked). Written without branches so that the lanes of a warp stay together up to the FM step.
+    const bool kindF = C.si_kind == GW_SI_F || C.si_kind == GW_SI_BD, kindB = C.si_kind == GW_SI_B || C.si_kind == GW_SI_BD;
     int viable = 0;
 #pragma unroll
-    for (int cand = 0; cand < 4; ++cand)
-        if (!((flags >> cand) & 1) && !gw_si_is_empty(&C, cand)) viable |= 1 << cand;
+    for (int cand = 0; cand < 4; ++cand) {
+        const bool nonempty = C.si_kind == GW_SI_B ? (((C.b_valid >> cand) & 1) && C.sib[cand][0] < C.sib[cand][1])
+                                                   : (kindF && ((C.f_valid >> cand) & 1) && C.sif[cand][0] < C.sif[cand][1]);
+        if (!((flags >> cand) & 1) && nonempty) viable |= 1 << cand;
+    }
     const bool own = ((viable >> nextBase) & 1) != 0;
     int ch;
     if (own) { ch = nextBase; flags |= 1 << nextBase; }
@@ -310,71 +298,185 @@ GW_HD int gw_search_try(const GwSearchEnv& env, const GwSlab& s, GwSearchLane& L
 #pragma unroll
         for (int cand = 3; cand >= 0; --cand) if ((viable >> cand) & 1) ch = cand;
         flags |= ((2 << ch) - 1) | (1 << nextBase);
-    } else { ch = -1; flags |= 0xF; }
-    if (ch < 0) {   // candidates exhausted without extending with the read's own base
-        flags |= 1 << 4;
-        Cp->state = flags;
-        if (DEFER) { L.mid = GW_MID_SPLIT; return GW_STEP_CONTINUE; }
-        L.mid = 0;
-        return gw_search_split(env, s, L);
+    } else { ch = -1; flags |= 0x1F; }
+    C.state = flags;
+    if (!exclusive) gw_st(s, ln.c_off)->state = flags;   // a fragment of a split chain can be reached through several heads
+    if (ch < 0) { ln.mid = GW_MID_SPLIT; return GW_STEP_CONTINUE; }   // candidates exhausted without extending with the read's own base
+    const u64* sf_tbl = gw_lane_staircase(env, s, ln);   // cannot fail here: gw_lane_poll checked it for this minMismatches
+    const int sf_kk = ln.min_mm;
+
+    // ---- Cursor.nextSi + bidirectionalSearch
+    bool hasF = kindF && ((C.f_valid >> ch) & 1), hasB = kindB && ((C.b_valid >> ch) & 1);
+    if (dir == GW_DIR_BF && C.cursor >= C.end - 1) hasF = false;
+    uint32_t f_lb = 0, f_ub = 0, b_lb = 0, b_ub = 0;   // intervals of `ch`, selected without indexing by a run-time value
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        if (i == ch) { f_lb = C.sif[i][0]; f_ub = C.sif[i][1]; b_lb = C.sib[i][0]; b_ub = C.sib[i][1]; }
+    GwState n;   // the child
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { n.sif[i][0] = n.sif[i][1] = 0; n.sib[i][0] = n.sib[i][1] = 0; }
+    n.f_valid = n.b_valid = 0;
+    n.si_kind = GW_SI_EMPTY;
+    if (hasF || hasB) {
+        const int fm = hasF ? (strand == 0 ? 1 : 0) : (strand == 0 ? 0 : 1);
+        const uint32_t lb = gw_clampN(ix, hasF ? f_lb : b_lb), ub = gw_clampN(ix, hasF ? f_ub : b_ub);
+        // both 64 B lines are requested before the first use, so that their misses overlap (the same line twice is one L1 miss)
+        const GwBlk bl = gw_load_block(ix.occ[fm] + (lb >> 7));
+        const GwBlk bu = gw_load_block(ix.occ[fm] + (ub >> 7));
+        uint32_t lo[4], hi[4];
+        gw_rank4(bl, lb & 127u, lo);
+        gw_rank4(bu, ub & 127u, hi);
+        uint8_t valid = 0;
+        uint32_t x = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t l = ix.C[fm][i] + lo[i], u = ix.C[fm][i] + hi[i];
+            if (hasF) { n.sif[i][0] = l; n.sif[i][1] = u; } else { n.sib[i][0] = l; n.sib[i][1] = u; }
+            if (l < u) valid |= (uint8_t)(1 << i);
+            if (hasF && hasB) {
+                const uint32_t y = hi[i] - lo[i];
+                n.sib[i][0] = b_lb + x; n.sib[i][1] = b_lb + x + y;
+                x += y;
+            }
+        }
+        if (hasF) { n.f_valid = valid; n.b_valid = hasB ? valid : 0; n.si_kind = hasB ? GW_SI_BD : GW_SI_F; }
+        else { n.b_valid = valid; n.si_kind = GW_SI_B; }
     }
-#if defined(__CUDA_ARCH__)
-    {   // the new state will be sifted up from the end of the queue: request the lines of its parent and grandparent
-        const int qn = c->qn;
-        const GwQEntry* q = s.queue();
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(q + ((qn - 1) >> 1)));
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(q + ((((qn - 1) >> 1) - 1) >> 1)));
+    ln.n_fm++;   // every bidirectionalSearch is two rank queries: occ_search is derived as 2 * n_fm when the read is emitted
+
+    // ---- ReadAlignmentNFA.nextState
+    const int m_read = ln.m;
+    const int height = C.height, kOffset = C.k_offset;
+    const int k = kOffset + height - 1;
+    const u64 qeq = gw_pattern_mask64(c, strand, m_read, fwdC, nextIdx, C.pivot, C.cursor, ch, k - kOffset);
+    const int fragmentLength = C.end - C.start;
+    const int progressIndex = fwdC ? C.cursor - C.pivot : C.end - C.cursor;
+    const int sf_offset = progressIndex - k;
+    const u64* prev = ln.rows;
+    u64 next[MAXH];
+    int minKwithMatch = k + 1, minKwithProgress = k + 1;
+    next[0] = (prev[0] & qeq) << 1;
+    if (next[0] != 0) { minKwithMatch = 0; minKwithProgress = 0; }
+    next[0] &= gw_staircase64(sf_tbl, m_read, sf_kk, kOffset, sf_offset);
+    const int mPos = k + fragmentLength - progressIndex;
+    int remove = -1;
+    bool hasMatch = false;
+    if constexpr (MAXH <= 8) {
+#pragma unroll
+        for (int i = 1; i < MAXH; ++i) {
+            if (i < height) {
+                u64 v = (prev[i] & qeq) << 1;
+                if (minKwithMatch > k && v != 0) minKwithMatch = i;
+                v |= prev[i - 1] | (prev[i - 1] << 1) | (next[i - 1] << 1);
+                v &= gw_staircase64(sf_tbl, m_read, sf_kk, kOffset + i, sf_offset);
+                if (minKwithProgress > k && (v & jshl(1ULL, height)) != 0) minKwithProgress = i;
+                next[i] = v;
+            } else next[i] = 0ULL;
+        }
+        if (mPos < 64) {
+#pragma unroll
+            for (int nm = MAXH - 1; nm >= 0; --nm)
+                if (nm < height && (next[nm] & jshl(1ULL, mPos)) != 0) { remove = nm; hasMatch = true; }
+        }
+    } else {
+#pragma unroll 1
+        for (int i = 1; i < height; ++i) {
+            u64 v = (prev[i] & qeq) << 1;
+            if (minKwithMatch > k && v != 0) minKwithMatch = i;
+            v |= prev[i - 1] | (prev[i - 1] << 1) | (next[i - 1] << 1);
+            v &= gw_staircase64(sf_tbl, m_read, sf_kk, kOffset + i, sf_offset);
+            if (minKwithProgress > k && (v & jshl(1ULL, height)) != 0) minKwithProgress = i;
+            next[i] = v;
+        }
+        if (mPos < 64) {
+            for (int nm = 0; nm < height; ++nm)
+                if ((next[nm] & jshl(1ULL, mPos)) != 0) { remove = nm; hasMatch = true; break; }
+        }
     }
-#endif
-    int kk;
-    const u64* tbl = gw_staircase_for(env, c, &kk);
-    u64 prev[MAXH];
-    {
-        const u64* rows = gw_rows(Cp);
+    if (remove < 0) {
+        const int minK = minKwithMatch < minKwithProgress ? minKwithMatch : minKwithProgress;
+        if (minK < k) remove = minK;
+        else { ln.n_filt++; return GW_STEP_CONTINUE; }   // no match: the candidate is dropped, the step goes on (ln.mid stays GW_MID_TRY)
+    }
+    const int newHeight = height - remove;
+    // the child of an extension with the read's own base replaces its parent (:426-429): when nothing else can refer to the parent,
+    // the child is built in the parent's slot
+    const int32_t off = (own && exclusive) ? ln.c_off : gw_lane_alloc_state(s, ln);
+    if (off < 0) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+    // Cursor.next
+    int nextCursor = C.cursor, d = dir;
+    if (d == GW_DIR_F) ++nextCursor;
+    else if (d == GW_DIR_B) --nextCursor;
+    else if (nextCursor + 1 < C.end) ++nextCursor;
+    else { d = GW_DIR_B; nextCursor = C.pivot; }
+    n.start = C.start; n.end = C.end; n.cursor = (int16_t)nextCursor; n.pivot = C.pivot;
+    n.cflag = (uint8_t)(strand | (d << 1));
+    // currentSi = nextCursor.isForwardSearch ? siTable.getForward(ch) : siTable.getBackward(ch)
+    const bool fwd = d != GW_DIR_B;
+    const bool has = fwd ? (kindF && ((C.f_valid >> ch) & 1)) : (kindB && ((C.b_valid >> ch) & 1));
+    n.has_cur = has ? 1 : 0;
+    n.cur_lb = has ? (fwd ? f_lb : b_lb) : 0;
+    n.cur_ub = has ? (fwd ? f_ub : b_ub) : 0;
+    n.height = (uint8_t)newHeight; n.k_offset = (uint8_t)(kOffset + remove); n.has_nfa = 1;
+    n.state = gw_pack_state(ch, kOffset + remove, gw_priority(&C), hasMatch);
+    n.next_split = C.next_split;
+    u64 nrows[MAXH];
+    if constexpr (MAXH <= 8) {
+        // remove == 0 keeps the OLD automaton (sic, ReadAlignmentNFA.java:206-207)
+#pragma unroll
+        for (int j = 0; j < MAXH; ++j) {
+            u64 v = 0ULL;
+#pragma unroll
+            for (int r = 0; r < MAXH - j; ++r)
+                if (r == remove) v = remove == 0 ? prev[j] : (next[j + r] >> 1);
+            nrows[j] = j < newHeight ? v : 0ULL;
+        }
+    } else {
+        if (remove == 0) { for (int h = 0; h < newHeight; ++h) nrows[h] = prev[h]; }
+        else { for (int h = 0; h < newHeight; ++h) nrows[h] = next[h + remove] >> 1; }
+    }
+    {   // written through to the arena
+        GwState* np = gw_st(s, off);
+        *np = n;
+        u64* nr = gw_rows(np);
         if constexpr (MAXH <= 8) {
 #pragma unroll
-            for (int i = 0; i < MAXH; ++i) prev[i] = i < C.height ? rows[i] : 0ULL;
+            for (int j = 0; j < MAXH; ++j) if (j < newHeight) nr[j] = nrows[j];
         } else {
-            for (int i = 0; i < C.height; ++i) prev[i] = rows[i];
+            for (int h = 0; h < newHeight; ++h) nr[h] = nrows[h];
         }
     }
-    GwSiSet nsi;
-    uint32_t lookups = 0;
-    gw_next_si(env.ix, &C, ch, &nsi, &lookups);
-    c->n_fm++;   // every bidirectionalSearch is two rank queries: occ_search is derived as 2 * n_fm when the read is emitted
-    GwState built;
-    const int32_t ns = gw_next_state<MAXH>(s, C, prev, ch, nsi, tbl, kk, &built);
-    if (ns == -2) { Cp->state = flags; gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
-    if (ns >= 0) {
-        // the usual case — a chain of one state — takes its queue key from the register copy of the state just built
-        const bool ok = (L.c_off == L.base && built.next_split < 0) ? gw_queue_add_key(s, ns, gw_state_key_single(cfg, &built))
-                                                                    : gw_queue_add(s, cfg, gw_update(s, L.base, L.c_off, ns));
-        if (!ok) { Cp->state = flags; gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
-        if (own) {   // extended: the parent is dropped (:426-429)
-            Cp->state = flags; L.mid = 0;
-#if defined(__CUDA_ARCH__)
-            // the step is over: the head of the queue is polled next; request its state now
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(s.at(s.queue()[0].off)));
-#endif
-            return GW_STEP_CONTINUE;
-        }
-    } else
-        c->n_filt++;
-    Cp->state = flags;
+    // the usual case — a chain of one state — takes its queue key from the register copy of the state just built
+    const bool ok = exclusive ? gw_lq_add(s, ln, off, gw_state_key_single(cfg, &n)) : gw_lane_chain_insert(env, s, ln, off);
+    if (!ok) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
+    if (own) {   // extended: the parent is dropped (:426-429), the step is over; the child is most likely the next state polled
+        ln.C = n;
+#pragma unroll
+        for (int j = 0; j < MAXH; ++j) ln.rows[j] = nrows[j];
+        ln.cached = off;
+        ln.mid = 0;
+    }
     return GW_STEP_CONTINUE;
 }
 
-// one whole iteration of the best-first loop (sequential form: the round-based search kernel and the host simulator)
-GW_HD int gw_step_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
-    GwSearchLane L;
-    int r = gw_search_poll(env, s, slot, rq, L);
-#pragma unroll 1
-    while (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try(env, s, L);
+// the out-of-line continuations of a step, on the work area (the lane is written back before and re-read after)
+template <int MAXH>
+GW_HD int gw_lane_split(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln) {
+    const bool exclusive = ln.c_off == ln.base && ln.C.next_split < 0;
+    ln.mid = 0;
+    gw_lane_flush(s, ln);
+    const int r = gw_search_split(env, s, ln.base, ln.c_off);
+    gw_lane_reload(s, ln);
+    ln.cached = -1;
+    if (exclusive) gw_lane_free_state(ln, ln.base);   // all its candidates are tried, its children are copies: unreachable from here on
     return r;
 }
-
-// Runs one read until it finishes or parks (sequential form of the two functions above).
-GW_HD void gw_run_read(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwRoundQueues& rq) {
-    int r = gw_resume_read(env, s, slot, rq);
-    while (r == GW_STEP_CONTINUE) r = gw_step_read(env, s, slot, rq);
+template <int MAXH>
+GW_HD int gw_lane_report(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln) {
+    ln.mid = 0;
+    gw_lane_flush(s, ln);
+    const int r = gw_search_report(env, s, ln.base);
+    gw_lane_reload(s, ln);
+    ln.cached = -1;
+    return r;
 }

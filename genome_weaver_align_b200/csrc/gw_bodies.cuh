@@ -1,10 +1,8 @@
-// gw_bodies.cuh — per-thread bodies of the batch kernels (prep, quick scan, locate, verify, emit).
-// Each function is the work of ONE thread of the kernel of the same name in gw_kernels.cu; the search-round body is
-// gw_run_read in gw_automaton.cuh. Reference methods replaced (align/src/main/java/org/utgenome/weaver/align/):
+// gw_bodies.cuh — per-thread bodies of the batch kernels (prep, quick scan, emit, settle).
+// Each function is the work of ONE thread of the kernel of the same name in gw_kernels.cu; the search / locate / verify path is
+// the flow kernel over gw_automaton.cuh and gw_job.cuh. Reference methods replaced (align/src/main/java/org/utgenome/weaver/align/):
 //   prep     BidirectionalSuffixFilter.AlignmentProcess ctor + N handling  strategy/BidirectionalSuffixFilter.java:189-198, :281-291
 //   scan     FMQuickScan.scanMismatchLocations                             strategy/FMQuickScan.java:66-94
-//   locate   FMIndexOnGenome.toCoordinate -> SparseSuffixArray.get         FMIndexOnGenome.java:227-252, SparseSuffixArray.java:141-161
-//   verify   AlignmentProcess.verify (window + alignBlockDetailed)         strategy/BidirectionalSuffixFilter.java:496-560
 //   emit     AlignmentProcess.align (choice of reported hits)              strategy/BidirectionalSuffixFilter.java:210-268
 #pragma once
 #include "gw_automaton.cuh"
@@ -41,7 +39,7 @@ GW_HD void gw_prep_read(const GwBatchView& bv, u64* slab_base, const GwSlabParam
     c->k = 0;
     c->max_match_len = 0; c->best_score = -1;
     c->n_fm = c->n_sw = c->n_cut = c->n_filt = 0;
-    c->qn = 0; c->n_hits = 0;
+    c->qn = 0; c->n_hits = 0; c->free1 = -1;
     c->top = (int32_t)s.arena_begin();
     c->pend_base = -1; c->pend_n = 0;
     c->sf_mm = -2; c->sf_off = -1;
@@ -113,51 +111,6 @@ GW_HD void gw_scan_task(const GwIndexView& ix, GwReadCtx* c, int strand) {
     c->scan_mm[strand] = numMismatches; c->scan_ls[strand] = ls; c->scan_le[strand] = le;
     c->scan_lb[strand] = lb; c->scan_ub[strand] = ub;
     gw_atomic_add(&c->occ_scan, 2u * (uint32_t)m);  // the two strands of a read are scanned by different threads
-}
-
-// ---- locate: one pending fragment ------------------------------------------------------------------------
-GW_HD void gw_locate_req(const GwIndexView& ix, u64* slab_base, uint32_t frag) {
-    GwReadCtx* c = reinterpret_cast<GwReadCtx*>(slab_base);
-    GwPendFrag* pf = &c->pend[frag];
-    uint32_t steps = 0;
-    pf->textpos = gw_sa_get(ix, pf->fm, pf->sa_index, &steps);
-    c->occ_locate += steps;
-}
-
-// ---- verify: one pending fragment ------------------------------------------------------------------------
-GW_HD void gw_verify_req(const GwIndexView& ix, u64* slab_base, uint32_t frag, int band_k, GwU64x2* hist, size_t stride) {
-    GwSlab s(slab_base);
-    GwReadCtx* c = s.ctx();
-    GwPendFrag* pf = &c->pend[frag];
-    const GwState* st = gw_st(s, pf->state_off);
-    const int strand = gw_strand(st);
-    const int start = st->start, end = st->end;
-    const int fragLen = end - start;
-    const int k = c->k;
-    const long long seqIndex = pf->fm == 0 ? (long long)pf->textpos : (long long)ix.N - (long long)pf->textpos;
-    const long long x = seqIndex - gw_head_offset(st);
-    long long refStart = x - k; if (refStart < 0) refStart = 0;
-    long long refEnd = x + fragLen + k; if (refEnd > (long long)ix.N) refEnd = (long long)ix.N;
-    pf->ref_start = refStart;
-    pf->res_abort = 0;
-    if (refStart > refEnd) { pf->res_abort = 1; pf->res_valid = 0; return; }  // ACGTSequence.subString throws
-    const int Ncols = (int)(refEnd - refStart);
-    // query fragment: q[strand][start, end), reversed on the reverse strand (:529-534)
-    const u64* qlo = c->qlo[strand];
-    const u64* qhi = c->qhi[strand];
-    auto qsym = [&](int i) -> int {
-        const int p = strand == 0 ? start + i : end - 1 - i;
-        return (int)((((qhi[p >> 6] >> (p & 63)) & 1ULL) << 1) | ((qlo[p >> 6] >> (p & 63)) & 1ULL));
-    };
-    u64 peq[4][GW_MAX_NB];
-    for (int a = 0; a < 4; ++a) for (int b = 0; b < GW_MAX_NB; ++b) peq[a][b] = 0;
-    for (int i = 0; i < fragLen; ++i) peq[qsym(i)][i >> 6] |= 1ULL << (i & 63);
-    const uint32_t r0 = (uint32_t)refStart;
-    auto refsym = [&](int j) -> int { return gw_ref_symbol(ix, r0 + (uint32_t)j); };
-    GwVerifyOut out;
-    gw_verify(fragLen, Ncols, band_k, peq, refsym, qsym, hist, stride, pf->cig, &out);
-    pf->res_valid = out.valid; pf->res_pos = out.pos; pf->res_diff = out.diff; pf->res_cig_n = out.cig_n;
-    if (out.cig_overflow) pf->res_abort = 2;  // cannot happen within GW_MAX_K; reported as unsupported
 }
 
 // ---- emit ------------------------------------------------------------------------------------------------
@@ -243,7 +196,7 @@ GW_HD void gw_settle(u64* big_base, u64* small_base, const GwSlabParams& small_s
     for (uint32_t i = 0; i < GW_CTX_WORDS; ++i) small_base[i] = big_base[i];
     sc->sp = small_sp;
     sc->ext = nullptr; sc->ext_pool = nullptr;
-    sc->qn = 0;
+    sc->qn = 0; sc->free1 = -1;
     sc->top = (int32_t)sm.arena_begin();
     const int nrep = gw_num_reported(bc, cfg);
     sc->n_hits = 0;

@@ -1,66 +1,9 @@
-// gw_fused.cuh — the whole per-read path as ONE resumable lane program: best-first search, SA locate and bit-vector DP
-// verification of a read are driven by the same lane, cut into short slices ("ticks") of one kind each. A warp runs, per
-// trip of its loop, the search slice for the lanes that are searching, the locate slice for those walking the suffix array,
-// the DP slice for those verifying, so every lane advances every trip and no read waits for a device-wide round.
-// Replaces the per-read sequence of AlignmentProcess.align_internal -> verify -> toCoordinate / alignBlockDetailed
-// (reference: align/src/main/java/org/utgenome/weaver/align/strategy/BidirectionalSuffixFilter.java:278-477, :496-560;
-// align/FMIndexOnGenome.java:227-252; align/SparseSuffixArray.java:141-161; align/BitParallelSmithWaterman.java:387-644).
+// gw_job.cuh — verification of one pending fragment of a parked read: reference window and pattern masks (AlignmentProcess.verify,
+// reference: align/src/main/java/org/utgenome/weaver/align/strategy/BidirectionalSuffixFilter.java:496-560), the bit-vector DP
+// columns and the traceback (align/BitParallelSmithWaterman.java:387-644, gw_verify.cuh), as three calls so that the lanes of a
+// verification batch run each part together.
 #pragma once
 #include "gw_bodies.cuh"
-
-#define GW_LP_FETCH 0    // lane has no read
-#define GW_LP_SEARCH 1   // one best-first iteration per tick
-#define GW_LP_LOCATE 2   // up to q_lf LF steps per tick
-#define GW_LP_DP 3       // up to q_cols DP columns per tick
-#define GW_LP_TRACE 4    // traceback + CIGAR of the finished DP
-
-struct GwFusedParams {
-    int32_t q_lf, q_cols;
-    int32_t stick;   // a warp keeps running its current kind of slice while 16 * (largest group) <= stick * (current group)
-};
-
-GW_HD GwRoundQueues gw_no_queues() {
-    GwRoundQueues rq;
-    rq.next_active = nullptr; rq.locate_req = nullptr; rq.verify_req = nullptr; rq.counters = nullptr;
-    return rq;
-}
-
-// picks the next pending fragment that needs locate (+ verify), or resumes the automaton with the results
-GW_COLD int gw_job_next(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, int from_frag) {
-    GwReadCtx* c = s.ctx();
-    for (;;) {
-        for (int f = from_frag; f < c->pend_n; ++f) {
-            if (c->pend[f].kind == 2) {
-                c->job.frag = f; c->job.lf_j = 0; c->job.lf_cursor = c->pend[f].sa_index;
-                return GW_LP_LOCATE;
-            }
-        }
-        const int r = gw_resume_read(env, s, slot, gw_no_queues());
-        if (r == GW_STEP_CONTINUE) return GW_LP_SEARCH;
-        if (r == GW_STEP_DONE) return GW_LP_FETCH;
-        from_frag = 0;   // parked again (exact hit waiting for its locate)
-    }
-}
-
-// a lane picked the read up: consumes the quick-scan results, seeds the queue (AlignmentProcess.align_internal :296-349)
-GW_HD int gw_fused_start(const GwSearchEnv& env, const GwSlab& s, uint32_t slot) {
-    const int r = gw_resume_read(env, s, slot, gw_no_queues());
-    if (r == GW_STEP_CONTINUE) return GW_LP_SEARCH;
-    if (r == GW_STEP_DONE) return GW_LP_FETCH;
-    return gw_job_next(env, s, slot, 0);
-}
-
-// search slice: (poll the queue unless the lane is in the middle of a step) + ONE candidate extension. All searching lanes of a warp
-// pass through the two sections together, whatever number of candidates their current step needs.
-GW_HD int gw_fused_search_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, GwSearchLane& L) {
-    int r = GW_STEP_CONTINUE;
-    if (!L.mid) r = gw_search_poll(env, s, slot, gw_no_queues(), L);
-    if (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try(env, s, L);
-    if (r == GW_STEP_CONTINUE) return GW_LP_SEARCH;
-    L.mid = 0;
-    if (r == GW_STEP_DONE) return GW_LP_FETCH;
-    return gw_job_next(env, s, slot, 0);
-}
 
 // 64 window columns starting at text position p (bit j = position p + j; positions >= N read as 0)
 GW_HD u64 gw_plane_window(const u64* plane, uint32_t n_words, uint32_t p) {
@@ -129,26 +72,6 @@ GW_HD int gw_job_ref_symbol(const GwJob* job, int j) {
     return (int)((((job->rw_hi[w] >> sft) & 1ULL) << 1) | ((job->rw_lo[w] >> sft) & 1ULL));
 }
 
-GW_HD int gw_fused_locate_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, const GwFusedParams& fp, GwU64x2* hist, size_t stride) {
-    GwReadCtx* c = s.ctx();
-    GwJob* job = &c->job;
-    GwPendFrag* pf = &c->pend[job->frag];
-    const GwIndexView& ix = env.ix;
-    uint32_t cursor = job->lf_cursor;
-    int j = job->lf_j;
-    for (int q = 0; q < fp.q_lf && (cursor % GW_SSA_L) != 0; ++q) {
-        cursor = gw_suffix_link(ix, pf->fm, cursor);
-        ++j;
-    }
-    if ((cursor % GW_SSA_L) != 0) { job->lf_cursor = cursor; job->lf_j = j; return GW_LP_LOCATE; }
-    const uint32_t smp = gw_ld32(ix.ssa[pf->fm] + cursor / GW_SSA_L);
-    pf->textpos = j == 0 ? smp : (uint32_t)(((u64)smp + (u64)j + ix.N) % ix.N);
-    c->occ_locate += (uint32_t)j;
-    if (c->phase == GW_PH_WAIT_EXACT) return gw_job_next(env, s, slot, c->pend_n);   // exact hit: no verification (:490-494)
-    if (gw_job_begin_dp(env, s, job, job->frag, hist, stride)) return GW_LP_DP;
-    return gw_job_next(env, s, slot, job->frag + 1);
-}
-
 // traceback + CIGAR of the fragment whose DP is complete; results go to its pending-fragment record
 GW_HD void gw_job_trace(const GwSlab& s, GwJob* job, const GwU64x2* hist, size_t stride) {
     GwReadCtx* c = s.ctx();
@@ -177,12 +100,6 @@ GW_HD void gw_job_trace(const GwSlab& s, GwJob* job, const GwU64x2* hist, size_t
     if (out.cig_overflow) pf->res_abort = 2;  // cannot happen within GW_MAX_K; reported as unsupported
 }
 
-GW_COLD int gw_fused_trace_tick(const GwSearchEnv& env, const GwSlab& s, uint32_t slot, GwU64x2* hist, size_t stride) {
-    GwJob* job = &s.ctx()->job;
-    gw_job_trace(s, job, hist, stride);
-    return gw_job_next(env, s, slot, job->frag + 1);
-}
-
 // DP columns [d.j, jEnd) of a job
 GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int n_cols, GwU64x2* hist, size_t stride, int nb_hint = 0) {
     GwDp d = job->dp;
@@ -204,19 +121,3 @@ GW_HD void gw_verify_frag(const GwSearchEnv& env, const GwSlab& s, GwJob* job, i
     gw_job_trace(s, job, hist, stride);
 }
 
-GW_HD int gw_fused_dp_tick(const GwSearchEnv& env, const GwSlab& s, const GwFusedParams& fp, GwU64x2* hist, size_t stride) {
-    GwJob* job = &s.ctx()->job;
-    gw_job_columns(env, job, fp.q_cols, hist, stride);
-    return job->dp.j >= job->dp.ncols ? GW_LP_TRACE : GW_LP_DP;
-}
-
-// one tick of whatever the lane is doing; returns the lane's next state
-GW_HD int gw_fused_tick(int lp, const GwSearchEnv& env, const GwSlab& s, uint32_t slot, GwSearchLane& L, const GwFusedParams& fp, GwU64x2* hist, size_t stride) {
-    switch (lp) {
-    case GW_LP_SEARCH: return gw_fused_search_tick(env, s, slot, L);
-    case GW_LP_LOCATE: return gw_fused_locate_tick(env, s, slot, fp, hist, stride);
-    case GW_LP_DP: return gw_fused_dp_tick(env, s, fp, hist, stride);
-    case GW_LP_TRACE: return gw_fused_trace_tick(env, s, slot, hist, stride);
-    default: return GW_LP_FETCH;
-    }
-}

@@ -1,21 +1,19 @@
 // gw_kernels.cu — the sm_100a kernels of the read-alignment path and their launchers.
 //
-//   kernel 1  gw_scan_coop_kernel   rank/occ + exact quick scan; 4 lanes share one 64 B occurrence block (one 128-bit
-//                                   load per lane), popcounts combined with warp shuffles   (FMQuickScan.java:66-94)
-//             gw_scan_kernel        single-thread form of the same scan (kept for A/B measurements)
-//   kernel 2  gw_search_kernel      per-read best-first bidirectional search automaton        (BidirectionalSuffixFilter.java:278-477)
-//   kernel 3  gw_locate_kernel      batched SA-sample locate (LF walk)                        (SparseSuffixArray.java:141-161)
-//   kernel 4  gw_verify_kernel      bit-vector DP verifier + CIGAR traceback                  (BitParallelSmithWaterman.java:387-644)
+//   kernel 1   gw_scan_coop_kernel   rank/occ + exact quick scan; 4 lanes share one 64 B occurrence block (one 128-bit
+//                                    load per lane), popcounts combined with warp shuffles   (FMQuickScan.java:66-94)
+//              gw_scan_kernel        single-thread form of the same scan (kept for A/B measurements)
+//   kernels 2-4 gw_flow_kernel       per-read best-first bidirectional search (BidirectionalSuffixFilter.java:278-477), SA locate
+//                                    (SparseSuffixArray.java:141-161) and bit-vector DP verification + CIGAR traceback
+//                                    (BitParallelSmithWaterman.java:387-644) as warp-wide work of one persistent kernel
 //   plus prep (read encoding), emit (hit records) and small utility kernels.
-// Grids are sized from the work-list length; every kernel is HBM/L2 random-access or integer-pipe bound (no tensor cores:
-// nothing here is a dense contraction).
+// Every kernel is HBM/L2 random-access or integer-pipe bound (no tensor cores: nothing here is a dense contraction).
 #include <cuda_runtime.h>
 
-#include "gw_fused.cuh"
+#include "gw_job.cuh"
 #include "gw_kernels.h"
 #include <stdlib.h>
 
-#define GW_SEARCH_THREADS 64
 
 // ---------------------------------------------------------------------------------------------------------
 __global__ void gw_prep_kernel(GwBatchView bv, u64* const* slabs, const uint32_t* slots, uint32_t n, uint32_t read_base, GwSlabParams sp) {
@@ -84,312 +82,37 @@ __global__ void __launch_bounds__(256) gw_scan_coop_kernel(GwIndexView ix, u64* 
     }
 }
 
-// Persistent lanes with work refill: every lane owns one read at a time and performs one best-first iteration per trip of
-// the outer loop; a lane whose read parks (needs locate/verify) or finishes takes the next read of the round's work list
-// (warp-aggregated atomic). Once the list is drained a running read gets `tail_steps` more iterations, then yields to the
-// next round, so the end of a launch is not held up by the few reads with very long searches.
-__global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_search_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
-                                                                      GwRoundQueues rq, uint32_t* work_counter, uint32_t tail_steps) {
-    const unsigned full = 0xFFFFFFFFu;
-    const unsigned lane = threadIdx.x & 31u;
-    bool have = false, exhausted = false;
-    GwSlab s;
-    uint32_t slot = 0, budget = tail_steps;
-    for (;;) {
-        const unsigned need = __ballot_sync(full, !have && !exhausted);
-        if (need) {
-            uint32_t first = 0;
-            const int leader = __ffs(need) - 1;
-            if ((int)lane == leader) first = atomicAdd(work_counter, (uint32_t)__popc(need));
-            first = __shfl_sync(full, first, leader);
-            if (!have && !exhausted) {
-                const uint32_t idx = first + (uint32_t)__popc(need & ((1u << lane) - 1u));
-                if (idx < n_active) {
-                    slot = active ? active[idx] : idx;
-                    s = GwSlab(slabs[slot]);
-                    have = gw_resume_read(env, s, slot, rq) == GW_STEP_CONTINUE;
-                    budget = tail_steps;
-                } else
-                    exhausted = true;
-            }
-        }
-        const unsigned busy = __ballot_sync(full, have);
-        const bool drained = __any_sync(full, exhausted);
-        if (!busy) {
-            if (drained) break;
-            continue;
-        }
-        if (have) {
-            if (gw_step_read(env, s, slot, rq) != GW_STEP_CONTINUE) have = false;
-            else if (drained && --budget == 0) { gw_yield_read(s, slot, rq); have = false; exhausted = true; }
-        }
-    }
-}
-
-// The whole per-read path on persistent lanes (gw_fused.cuh): a lane owns one read from its first search step to its last
-// verification. Per trip of the warp loop the lanes that search run one best-first iteration, those locating run a few LF
-// steps, those verifying a slice of DP columns; a lane whose read is finished takes the next one from the work list.
-__global__ void __launch_bounds__(GW_SEARCH_THREADS) gw_fused_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
-                                                                     uint32_t* work_counter, GwU64x2* hist, GwFusedParams fp, const uint32_t* n_active_dev) {
-    const unsigned full = 0xFFFFFFFFu;
-    if (n_active_dev) n_active = *n_active_dev;   // list length produced on the device (leftovers of the pool kernel)
-    const unsigned lane = threadIdx.x & 31u;
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int lp = GW_LP_FETCH, mode = GW_LP_SEARCH;
-    bool exhausted = false;
-    GwSlab s;
-    GwSearchLane L;
-    L.base = L.c_off = -1; L.mid = 0;
-    uint32_t slot = 0;
-    for (;;) {
-        const unsigned need = __ballot_sync(full, lp == GW_LP_FETCH && !exhausted);
-        if (need) {
-            uint32_t first = 0;
-            const int leader = __ffs(need) - 1;
-            if ((int)lane == leader) first = atomicAdd(work_counter, (uint32_t)__popc(need));
-            first = __shfl_sync(full, first, leader);
-            if (lp == GW_LP_FETCH && !exhausted) {
-                const uint32_t idx = first + (uint32_t)__popc(need & ((1u << lane) - 1u));
-                if (idx < n_active) {
-                    slot = active ? active[idx] : idx;
-                    s = GwSlab(slabs[slot]);
-                    L.mid = 0;
-                    lp = gw_fused_start(env, s, slot);
-                } else
-                    exhausted = true;
-            }
-        }
-        // The warp runs ONE kind of slice per trip — the kind most of its lanes are waiting for — so the lanes that execute
-        // together follow the same code; lanes in another stage wait until their stage has the majority (or the current one
-        // has drained). `mode` is warp-uniform, so the dispatch below does not diverge.
-        const int cS = __popc(__ballot_sync(full, lp == GW_LP_SEARCH)), cL = __popc(__ballot_sync(full, lp == GW_LP_LOCATE));
-        const int cD = __popc(__ballot_sync(full, lp == GW_LP_DP)), cT = __popc(__ballot_sync(full, lp == GW_LP_TRACE));
-        if (cS + cL + cD + cT == 0) {
-            if (__all_sync(full, exhausted)) break;
-            continue;
-        }
-        int best = cS, bm = GW_LP_SEARCH;
-        if (cL > best) { best = cL; bm = GW_LP_LOCATE; }
-        if (cD > best) { best = cD; bm = GW_LP_DP; }
-        if (cT > best) { best = cT; bm = GW_LP_TRACE; }
-        const int cur = mode == GW_LP_SEARCH ? cS : mode == GW_LP_LOCATE ? cL : mode == GW_LP_DP ? cD : mode == GW_LP_TRACE ? cT : 0;
-        if (cur * fp.stick < best * 16 || cur == 0) mode = bm;   // leave the current kind of slice only for a clearly larger group
-        if (mode == GW_LP_SEARCH) { if (lp == GW_LP_SEARCH) lp = gw_fused_search_tick(env, s, slot, L); }
-        else if (mode == GW_LP_LOCATE) { if (lp == GW_LP_LOCATE) lp = gw_fused_locate_tick(env, s, slot, fp, my_hist, stride); }
-        else if (mode == GW_LP_DP) { if (lp == GW_LP_DP) lp = gw_fused_dp_tick(env, s, fp, my_hist, stride); }
-        else { if (lp == GW_LP_TRACE) lp = gw_fused_trace_tick(env, s, slot, my_hist, stride); }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------------------
-// Block-level pool: a CTA keeps up to GW_POOL reads in flight and advances them in three phases separated by CTA barriers —
-//   S  search slices for the reads that can search (lanes take reads from a shared list; a read that needs verification, or
-//      that used up its step budget, goes to the next round's list),
-//   L  SA locate of the fragments waiting for verification (one LF walk per fragment),
-//   D  bit-vector DP + traceback of those fragments —
-// so that the lanes running together always execute the same kind of work, without device-wide rounds: CTAs are not
-// synchronised with each other and refill their pool from the global work list as reads finish. When the work list is
-// drained and a pool has shrunk below `tail_thr` reads, the CTA hands its remaining reads to the leftover list (they are
-// finished by gw_fused_kernel, whose lanes are independent).
-#ifndef GW_POOL_THREADS
-#define GW_POOL_THREADS 256
-#endif
-#ifndef GW_POOL_MINB
-#define GW_POOL_MINB 2
-#endif
-#define GW_POOL 1024
-
-struct GwPoolParams {
-    uint32_t budget;     // search slices per read and round
-    uint32_t tail_thr;   // pool size below which the CTA hands over
-    uint32_t taper;      // slices shrink over the last taper x blockDim reads of a phase (0: off)
-    uint32_t cap;        // reads a CTA keeps in flight (<= GW_POOL): small work lists are spread over all CTAs of the grid
-    uint32_t batch;      // warp pools: lanes that must wait for a deferred continuation before the warp runs it
-    uint32_t age;        // warp pools: ... or this many trips since the first lane started waiting
-    uint32_t flush;      // flow kernel: once the work list is drained, a partial verification batch runs when this many lanes idle
-};
-
-#ifdef GW_POOL_PROF
-// phase accounting of the pool kernel (diagnostic builds only): thread-cycles spent working / waiting at the barrier, per phase
-__device__ unsigned long long gw_pool_prof[8];
-#define GW_PROF_T(v) const long long v = clock64()
-#define GW_PROF_ADD(i, d) prof[i] += (unsigned long long)(d)
-extern "C" int gw_debug_pool_prof(unsigned long long* out, int reset) {
-    cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(out, gw_pool_prof, sizeof(gw_pool_prof));
-    if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(gw_pool_prof, z, sizeof(z)); }
-    return 0;
-}
-#else
-#define GW_PROF_T(v)
-#define GW_PROF_ADD(i, d)
-#endif
-template <int MAXH>
-__global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_pool_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
-                                                                  uint32_t* work_counter, GwU64x2* hist, GwPoolParams pp, uint32_t* leftover,
-                                                                  uint32_t* leftover_count) {
-    __shared__ uint32_t ready[2][GW_POOL];       // reads to resume / continue, this round and the next
-    __shared__ uint32_t frags[2 * GW_POOL];      // slot * 2 + fragment waiting for locate (+ verify)
-    __shared__ uint32_t n_ready[2], n_frags, head, pool, drained, cur, refill_first, refill_base, refill_n, lo_base;
-    const uint32_t tid = threadIdx.x;
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + tid;
-    const GwRoundQueues noq = gw_no_queues();
-    if (tid == 0) { n_ready[0] = n_ready[1] = 0; n_frags = 0; pool = 0; drained = 0; cur = 0; }
-    __syncthreads();
-#ifdef GW_POOL_PROF
-    unsigned long long prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-#endif
-    for (;;) {
-        GW_PROF_T(t_round);
-        // ---- refill the pool from the global work list
-        if (tid == 0) {
-            head = 0; refill_n = 0;
-            n_ready[cur ^ 1] = 0; n_frags = 0;
-            if (!drained && pool < pp.cap) {
-                const uint32_t want = pp.cap - pool;
-                const uint32_t first = atomicAdd(work_counter, want);
-                uint32_t got = 0;
-                if (first < n_active) got = min(want, n_active - first);
-                if (first + want >= n_active) drained = 1;
-                refill_first = first; refill_base = n_ready[cur]; refill_n = got;
-                n_ready[cur] += got; pool += got;
-            }
-        }
-        __syncthreads();
-        for (uint32_t i = tid; i < refill_n; i += blockDim.x) ready[cur][refill_base + i] = active ? active[refill_first + i] : refill_first + i;
-        const uint32_t c_idx = cur, n_idx = cur ^ 1u;
-        const uint32_t nr = n_ready[c_idx];
-        if (pool == 0) break;
-        if (drained && pool < pp.tail_thr) {   // hand the stragglers over
-            if (tid == 0) lo_base = atomicAdd(leftover_count, nr);
-            __syncthreads();
-            for (uint32_t i = tid; i < nr; i += blockDim.x) leftover[lo_base + i] = ready[c_idx][i];
-            break;
-        }
-        __syncthreads();
-        GW_PROF_T(t_s0);
-        GW_PROF_ADD(6, t_s0 - t_round);
-        // ---- phase S
-        {
-            bool have = false;
-            GwSlab s;
-            GwSearchLane L;
-            L.base = L.c_off = -1; L.mid = 0;
-            uint32_t slot = 0, budget = 0;
-            for (;;) {
-                if (!have) {
-                    const uint32_t i = atomicAdd(&head, 1u);
-                    if (i >= nr) break;
-                    slot = ready[c_idx][i];
-                    s = GwSlab(slabs[slot]);
-                    L.mid = 0;
-                    // the last reads of the list get shorter slices, so that the lanes reach the barrier together (a read whose
-                    // slice ends simply continues in the next round)
-                    budget = pp.budget;
-                    if (pp.taper) { const uint32_t rem = nr - i, span = pp.taper * blockDim.x; if (rem < span) budget = max(pp.budget * rem / span, 4u); }
-                    const int r0 = gw_resume_read(env, s, slot, noq);
-                    if (r0 == GW_STEP_DONE) { atomicSub(&pool, 1u); continue; }
-                    if (r0 == GW_STEP_PARKED) {   // exact hit: needs its locate only
-                        ready[n_idx][atomicAdd(&n_ready[n_idx], 1u)] = slot;
-                        frags[atomicAdd(&n_frags, 1u)] = slot * 2u;
-                        continue;
-                    }
-                    have = true;
-                }
-                int r = GW_STEP_CONTINUE;
-                if (!L.mid) {
-                    if (gw_wants_promotion(s)) gw_promote(s, const_cast<u64**>(slabs) + slot);   // nearly full: go on in a larger work area
-                    r = gw_search_poll(env, s, slot, noq, L);
-                }
-                if (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try<false, MAXH>(env, s, L);
-                if (r == GW_STEP_CONTINUE) {
-                    if (--budget == 0 && !L.mid) { ready[n_idx][atomicAdd(&n_ready[n_idx], 1u)] = slot; have = false; }
-                    else if (budget == 0) budget = 1;   // finish the step that is under way
-                } else if (r == GW_STEP_DONE) { atomicSub(&pool, 1u); have = false; }
-                else {   // parked with a verification request
-                    const GwReadCtx* c = s.ctx();
-                    ready[n_idx][atomicAdd(&n_ready[n_idx], 1u)] = slot;
-                    for (int f = 0; f < c->pend_n; ++f)
-                        if (c->pend[f].kind == 2) frags[atomicAdd(&n_frags, 1u)] = slot * 2u + (uint32_t)f;
-                    have = false;
-                }
-            }
-        }
-        GW_PROF_T(t_s1);
-        __syncthreads();
-        if (tid == 0) head = 0;
-        __syncthreads();
-        GW_PROF_T(t_l0);
-        GW_PROF_ADD(0, t_s1 - t_s0); GW_PROF_ADD(1, t_l0 - t_s1); GW_PROF_ADD(7, 1);
-        const uint32_t nf = n_frags;
-        // ---- phase L: lanes stay in the LF loop and take the next fragment when their walk ends
-        {
-            bool have = false;
-            GwPendFrag* pf = nullptr;
-            GwReadCtx* c = nullptr;
-            uint32_t cursor = 0;
-            int j = 0, fm = 0;
-            for (;;) {
-                if (!have) {
-                    const uint32_t i = atomicAdd(&head, 1u);
-                    if (i >= nf) break;
-                    const uint32_t id = frags[i];
-                    c = reinterpret_cast<GwReadCtx*>(slabs[id >> 1]);
-                    pf = &c->pend[id & 1u];
-                    cursor = pf->sa_index; fm = pf->fm; j = 0;
-                    have = true;
-                }
-                if ((cursor % GW_SSA_L) != 0) { cursor = gw_suffix_link(env.ix, fm, cursor); ++j; }
-                if ((cursor % GW_SSA_L) == 0) {
-                    const uint32_t smp = gw_ld32(env.ix.ssa[fm] + cursor / GW_SSA_L);
-                    pf->textpos = j == 0 ? smp : (uint32_t)(((u64)smp + (u64)j + env.ix.N) % env.ix.N);
-                    atomicAdd(&c->occ_locate, (uint32_t)j);   // the two fragments of a read may be walked by different lanes
-                    have = false;
-                }
-            }
-        }
-        GW_PROF_T(t_l1);
-        __syncthreads();
-        GW_PROF_T(t_d0);
-        GW_PROF_ADD(2, t_l1 - t_l0); GW_PROF_ADD(3, t_d0 - t_l1);
-        // ---- phase D
-        for (uint32_t i = tid; i < nf; i += blockDim.x) {
-            const uint32_t id = frags[i];
-            GwSlab s(slabs[id >> 1]);
-            if (s.ctx()->phase == GW_PH_WAIT_EXACT) continue;   // exact hit: no verification (:490-494)
-            GwJob job;
-            gw_verify_frag(env, s, &job, (int)(id & 1u), my_hist, stride);
-        }
-        GW_PROF_T(t_d1);
-        __syncthreads();
-        if (tid == 0) cur = n_idx;
-        __syncthreads();
-        GW_PROF_T(t_e);
-        GW_PROF_ADD(4, t_d1 - t_d0); GW_PROF_ADD(5, t_e - t_d1);
-    }
-#ifdef GW_POOL_PROF
-    for (int i = 0; i < 8; ++i) atomicAdd(&gw_pool_prof[i], prof[i]);
-#endif
-}
-
 // ---------------------------------------------------------------------------------------------------------
 // Flow kernel: warp-level pools without rounds. Every warp owns two small FIFOs in shared memory — reads ready to (re)start
 // searching and fragments waiting for locate + verification — and loops over three kinds of warp-wide work:
-//   * search slices: one poll + one candidate extension per lane and trip; the long, rarely taken continuations (taking a read up /
-//     consuming verification results, split + soft-clip children, chain reporting) are deferred until `batch` lanes wait for one
-//     (or `age` trips passed, or nothing else can run), so that they run for several lanes at once instead of one lane while 31 wait,
+//   * search slices: one poll + one candidate extension per lane and trip, on the lane's register copy of its read (GwLane); the
+//     long, rarely taken continuations (taking a read up / consuming verification results, split + soft-clip children, chain
+//     reporting) are deferred until `batch` lanes wait for one (or `age` trips passed, or nothing else can run), so that they run
+//     for several lanes at once instead of one lane while 31 wait,
 //   * pick-up: idle lanes take reads from the ready FIFO (refilled from the global work list, `cap` reads at a time),
 //   * a verification batch as soon as 32 fragments wait: every lane walks one fragment to its SA sample and runs its DP + traceback;
 //     the reads whose fragments are all done go back to the ready FIFO.
 // There is no per-round tail: a lane that parks or finishes a read takes the next one at once, and locate / DP always run with
 // (nearly) full warps.
+#ifndef GW_FLOW_THREADS
+#define GW_FLOW_THREADS 256
+#endif
+#ifndef GW_FLOW_MINB
+#define GW_FLOW_MINB 2
+#endif
 #define GW_RING 128     // entries per FIFO; a warp owns at most GW_RING reads (refill stops above GW_RING - 32), at most 95 fragments wait
-#define GW_WARPS (GW_POOL_THREADS / 32)
+#define GW_WARPS (GW_FLOW_THREADS / 32)
+
+struct GwFlowParams {
+    uint32_t cap;        // reads a warp takes from the work list at a time
+    uint32_t batch;      // lanes that must wait for a deferred continuation before the warp runs it
+    uint32_t age;        // ... or this many trips since the first lane started waiting
+    uint32_t flush;      // once the work list is drained, a partial verification batch runs when this many lanes idle
+};
+
 template <int MAXH>
-__global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
-                                                                  uint32_t* work_counter, GwU64x2* hist, GwPoolParams pp) {
+__global__ void __launch_bounds__(GW_FLOW_THREADS, GW_FLOW_MINB) gw_flow_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
+                                                                  uint32_t* work_counter, GwU64x2* hist, GwFlowParams pp) {
     __shared__ uint32_t ready_s[GW_WARPS][GW_RING];
     __shared__ uint32_t frags_s[GW_WARPS][GW_RING];
     const uint32_t FULL = 0xFFFFFFFFu, MASK = GW_RING - 1u;
@@ -399,13 +122,12 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
     uint32_t* frags = frags_s[wid];
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const GwRoundQueues noq = gw_no_queues();
     uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_pick = 0, age_cold = 0, owned = 0;
     bool drained = false;
     bool have = false;
     GwSlab s;
-    GwSearchLane L;
-    L.base = L.c_off = -1; L.mid = 0;
+    GwLane<MAXH> ln;
+    ln.mid = 0; ln.top = 0; ln.k = 0;
     uint32_t slot = 0;
     for (;;) {
         const uint32_t busy = __ballot_sync(FULL, have);
@@ -475,9 +197,9 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
                     if (i < nrd) {
                         slot = ready[(r_head + i) & MASK];
                         s = GwSlab(slabs[slot]);
-                        L.mid = 0;
-                        r0 = gw_resume_read(env, s, slot, noq);
+                        r0 = gw_resume_read(env, s);
                         have = r0 == GW_STEP_CONTINUE;
+                        if (have) gw_lane_load(s, ln);
                     }
                 }
                 r_head += min((uint32_t)__popc(idle), nrd);
@@ -494,11 +216,12 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
         // ---- one search slice per lane
         int r = GW_STEP_CONTINUE;
         {   // work areas that are nearly full: the reads go on in a larger one; the lanes of the warp share each copy
-            const bool wantp = have && L.mid == 0 && gw_wants_promotion(s);
+            const bool wantp = have && ln.mid == 0 && gw_wants_promotion(s, (uint32_t)ln.top, ln.k);
             if (__ballot_sync(FULL, wantp) != 0u) {
+                if (wantp) gw_lane_flush(s, ln);   // the copy takes the work area as it is in HBM
                 u64* nb = wantp ? gw_promote_take(s) : nullptr;
                 uint32_t pm = __ballot_sync(FULL, nb != nullptr);
-                const uint32_t my_top = nb ? (uint32_t)s.ctx()->top : 0u;
+                const uint32_t my_top = nb ? (uint32_t)ln.top : 0u;
                 while (pm) {
                     const int src = __ffs(pm) - 1;
                     pm &= pm - 1u;
@@ -511,27 +234,29 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
                 if (nb) gw_promote_commit(s, nb, const_cast<u64**>(slabs) + slot);
             }
         }
-        if (have && L.mid == 0) r = gw_search_poll<true>(env, s, slot, noq, L);
-        if (have && r == GW_STEP_CONTINUE && L.mid == GW_MID_TRY) r = gw_search_try<true, MAXH>(env, s, L);
+        if (have && ln.mid == 0) r = gw_lane_poll(env, s, ln);
+        if (have && r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY) r = gw_lane_try(env, s, ln);
         // ---- deferred continuations
         {
-            const bool wants = have && r == GW_STEP_CONTINUE && L.mid >= GW_MID_SPLIT;
+            const bool wants = have && r == GW_STEP_CONTINUE && ln.mid >= GW_MID_SPLIT;
             const uint32_t cold = __ballot_sync(FULL, wants);
             if (cold != 0u) {
-                const uint32_t hot = __ballot_sync(FULL, have && r == GW_STEP_CONTINUE && L.mid < GW_MID_SPLIT);
+                const uint32_t hot = __ballot_sync(FULL, have && r == GW_STEP_CONTINUE && ln.mid < GW_MID_SPLIT);
                 if ((uint32_t)__popc(cold) >= pp.batch || hot == 0u || ++age_cold >= pp.age) {
                     age_cold = 0;
-                    if (wants && L.mid == GW_MID_SPLIT) { L.mid = 0; r = gw_search_split(env, s, L); }
-                    if (wants && L.mid == GW_MID_REPORT) { L.mid = 0; r = gw_search_report(env, s, slot, noq, L.base); }
+                    if (wants) r = ln.mid == GW_MID_SPLIT ? gw_lane_split(env, s, ln) : gw_lane_report(env, s, ln);
                 }
             }
         }
         // ---- parked reads queue their fragments (both fragments of a read next to each other); finished reads just leave
         bool f0 = false, f1 = false;
-        if (have && r == GW_STEP_PARKED) {
-            const GwReadCtx* c = s.ctx();
-            f0 = c->pend_n > 0 && c->pend[0].kind == 2;
-            f1 = c->pend_n > 1 && c->pend[1].kind == 2;
+        if (have && r != GW_STEP_CONTINUE) {
+            gw_lane_flush(s, ln);
+            if (r == GW_STEP_PARKED) {
+                const GwReadCtx* c = s.ctx();
+                f0 = c->pend_n > 0 && c->pend[0].kind == 2;
+                f1 = c->pend_n > 1 && c->pend[1].kind == 2;
+            }
         }
         const uint32_t b_f0 = __ballot_sync(FULL, f0), b_f1 = __ballot_sync(FULL, f1);
         if (b_f0 | b_f1) {
@@ -544,20 +269,6 @@ __global__ void __launch_bounds__(GW_POOL_THREADS, GW_POOL_MINB) gw_flow_kernel(
         owned -= (uint32_t)__popc(__ballot_sync(FULL, have && r == GW_STEP_DONE));
         if (have && r != GW_STEP_CONTINUE) have = false;
     }
-}
-
-__global__ void gw_locate_kernel(GwIndexView ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    uint32_t id = req[i];
-    gw_locate_req(ix, slabs[id >> 1], id & 1u);
-}
-
-__global__ void gw_verify_kernel(GwIndexView ix, u64* const* slabs, const uint32_t* req, uint32_t n, int band_k, GwU64x2* hist) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    uint32_t id = req[i];
-    gw_verify_req(ix, slabs[id >> 1], id & 1u, band_k, hist + i, (size_t)n);
 }
 
 // collects the slots whose slab overflowed (rerun with the large slab)
@@ -737,63 +448,23 @@ void gwk_scan(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const u
     if (coop) gw_scan_coop_kernel<<<gw_grid(n_tasks * 4, 256), 256, 0, st>>>(ix, slabs, slots, (uint32_t)n_tasks);
     else gw_scan_kernel<<<gw_grid(n_tasks, 128), 128, 0, st>>>(ix, slabs, slots, (uint32_t)n_tasks);
 }
-void gwk_search(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, const GwRoundQueues& rq,
-                uint32_t* work_counter, uint32_t tail_steps, uint32_t max_blocks) {
-    if (!n_active) return;
-    unsigned blocks = gw_grid(n_active, GW_SEARCH_THREADS);
-    if (blocks > max_blocks) blocks = max_blocks;
-    gw_search_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, rq, work_counter, tail_steps);
-}
-void gwk_fused(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-               int q_lf, int q_cols, int stick, uint32_t blocks, const uint32_t* n_active_dev) {
-    if (!n_active) return;
-    GwFusedParams fp;
-    fp.q_lf = q_lf; fp.q_cols = q_cols; fp.stick = stick;
-    gw_fused_kernel<<<blocks, GW_SEARCH_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, fp, n_active_dev);
-}
-void gwk_pool(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-              uint32_t budget, uint32_t tail_thr, uint32_t cap, uint32_t taper, uint32_t blocks, uint32_t* leftover, uint32_t* leftover_count, int maxh) {
-    if (!n_active) return;
-    GwPoolParams pp;
-    pp.batch = pp.age = pp.flush = 1;
-    pp.taper = taper;
-    pp.budget = budget; pp.tail_thr = tail_thr; pp.cap = cap < 1 ? 1 : (cap > GW_POOL ? GW_POOL : cap);
-    static bool carved = false;   // the lists need 17 KB per CTA: leave the rest of the SM's 256 KB to the L1 (per-read work areas)
-    if (!carved) {
-        const int pct = getenv("GW_CARVEOUT") ? atoi(getenv("GW_CARVEOUT")) : 28;
-        cudaFuncSetAttribute(gw_pool_kernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-        cudaFuncSetAttribute(gw_pool_kernel<8>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-        cudaFuncSetAttribute(gw_pool_kernel<GW_MAX_ROWS>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-        carved = true;
-    }
-    if (maxh <= 4) gw_pool_kernel<4><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
-    else if (maxh <= 8) gw_pool_kernel<8><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
-    else gw_pool_kernel<GW_MAX_ROWS><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp, leftover, leftover_count);
+void gwk_flow_setup(void) {
+    // two CTAs need 18 KB for their FIFOs: the smallest fitting shared-memory configuration leaves 224 KB of each SM to the L1, where
+    // the per-read work areas live. Function attributes are per device: called once per aligner (after cudaSetDevice).
+    const int pct = 14;
+    cudaFuncSetAttribute(gw_flow_kernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+    cudaFuncSetAttribute(gw_flow_kernel<8>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+    cudaFuncSetAttribute(gw_flow_kernel<GW_MAX_ROWS>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
 }
 void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
               uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh) {
     if (!n_active) return;
-    GwPoolParams pp;
-    pp.taper = 0; pp.budget = 0; pp.tail_thr = 0;
+    GwFlowParams pp;
     pp.cap = fetch < 1 ? 1 : (fetch > 32 ? 32 : fetch);
     pp.batch = batch < 1 ? 1 : batch; pp.age = age < 1 ? 1 : age; pp.flush = flush < 1 ? 1 : flush;
-    static bool carved = false;   // two CTAs need 18 KB for their FIFOs: the smallest fitting configuration leaves 224 KB of L1
-    if (!carved) {
-        const int pct = getenv("GW_CARVEOUT") ? atoi(getenv("GW_CARVEOUT")) : 14;
-        cudaFuncSetAttribute(gw_flow_kernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-        cudaFuncSetAttribute(gw_flow_kernel<8>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-        cudaFuncSetAttribute(gw_flow_kernel<GW_MAX_ROWS>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-        carved = true;
-    }
-    if (maxh <= 4) gw_flow_kernel<4><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
-    else if (maxh <= 8) gw_flow_kernel<8><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
-    else gw_flow_kernel<GW_MAX_ROWS><<<blocks, GW_POOL_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
-}
-void gwk_locate(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n) {
-    if (n) gw_locate_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, slabs, req, n);
-}
-void gwk_verify(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n, int band_k, void* hist) {
-    if (n) gw_verify_kernel<<<gw_grid(n, 128), 128, 0, st>>>(ix, slabs, req, n, band_k, (GwU64x2*)hist);
+    if (maxh <= 4) gw_flow_kernel<4><<<blocks, GW_FLOW_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
+    else if (maxh <= 8) gw_flow_kernel<8><<<blocks, GW_FLOW_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
+    else gw_flow_kernel<GW_MAX_ROWS><<<blocks, GW_FLOW_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
 }
 void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count) {
     if (n) gw_collect_overflow_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, list, count);

@@ -7,16 +7,9 @@
 void gwk_fill_slab_ptrs(cudaStream_t st, u64** slabs, u64* base, size_t slab_words, const uint32_t* slots, uint32_t n);
 void gwk_prep(cudaStream_t st, const GwBatchView& bv, u64* const* slabs, const uint32_t* slots, uint32_t n, uint32_t read_base, const GwSlabParams& sp);
 void gwk_scan(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* slots, uint32_t n_slots, int coop);
-void gwk_search(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, const GwRoundQueues& rq,
-                uint32_t* work_counter, uint32_t tail_steps, uint32_t max_blocks);
-void gwk_fused(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-               int q_lf, int q_cols, int stick, uint32_t blocks, const uint32_t* n_active_dev);
-void gwk_pool(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-              uint32_t budget, uint32_t tail_thr, uint32_t cap, uint32_t taper, uint32_t blocks, uint32_t* leftover, uint32_t* leftover_count, int maxh);
+void gwk_flow_setup(void);   // per-device function attributes of the flow kernel
 void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
               uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh);
-void gwk_locate(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n);
-void gwk_verify(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* req, uint32_t n, int band_k, void* hist);
 void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count);
 void gwk_settle(cudaStream_t st, u64** slabs, u64* small_base, size_t small_words, const GwSlabParams& small_sp, const uint32_t* list, uint32_t n, const GwDevConfig& cfg);
 void gwk_emit_count(cudaStream_t st, u64* const* slabs, uint32_t n, const GwDevConfig& cfg, uint32_t* n_rec, uint32_t* n_cig, unsigned long long* totals,

@@ -109,9 +109,12 @@ GW_HD int32_t gw_queue_poll(const GwSlab& s, const GwDevConfig& cfg) {
     return result;
 }
 
-// allocate a state with `height` NFA rows; fields are filled by the caller
+// allocate a state (room for the read's full NFA height whatever `height` is: see gw_state_words); fields are filled by the caller
 GW_HD int32_t gw_alloc_state(const GwSlab& s, int height) {
-    return gw_alloc(s, GW_STATE_WORDS + (uint32_t)height);
+    (void)height;
+    GwReadCtx* c = s.ctx();
+    if (c->free1 >= 0) { const int32_t o = c->free1; c->free1 = -1; return o; }
+    return gw_alloc(s, gw_state_words(c->k));
 }
 // whole-state copy from / to the arena (six 128-bit accesses; states are 16-byte aligned)
 GW_HD GwState gw_load_state(const GwSlab& s, int32_t off) { return *gw_st(s, off); }
@@ -155,162 +158,138 @@ GW_HD bool gw_si_is_empty(const GwState* c, int ch) {
     return !((c->f_valid >> ch) & 1) || c->sif[ch][0] >= c->sif[ch][1];
 }
 
-struct GwSiSet {
-    uint8_t kind, f_valid, b_valid;
-    uint32_t sif[4][2], sib[4][2];
+// ---- search lane -------------------------------------------------------------------------------------------
+// A lane (one thread) drives one read at a time. What every step of the best-first loop touches lives in the lane's registers
+// while the lane owns the read: the counters and cursors of the context, the root of the priority queue, and the state that is
+// being extended (`C`, with its NFA rows). The work area in HBM stays the canonical copy for everything else; the lane's copy is
+// written back (gw_lane_flush) before any of the out-of-line continuations runs on the work area and re-read after it
+// (gw_lane_reload). States are written through to the arena when they are built, so `cached` only ever saves the load:
+// after an extension with the read's own base the child is the next state polled nearly every time, and it is already here.
+template <int MAXH>
+struct GwLane {
+    int32_t m, k, min_mm, best_score;
+    int32_t n_fm, n_cut, n_filt;
+    int32_t qn, top, free1;
+    int32_t sf_mm, sf_off;      // staircase table of minMismatches == sf_mm: word offset, -1: the reference throws
+    u64 root_key;               // queue entry 0 (valid while qn > 0)
+    int32_t root_off;
+    int32_t base;               // polled queue entry (head of the split chain)
+    int32_t c_off;              // fragment of the chain that is being extended
+    int32_t mid;                // GW_MID_*: what remains of the current step
+    int32_t cached;             // arena offset whose state C / rows hold, -1: none
+    GwState C;
+    u64 rows[MAXH];
 };
 
-// Cursor.nextSi + FMIndexOnGenome.bidirectionalSearch: two rank queries on one index
-GW_HD void gw_next_si(const GwIndexView& ix, const GwState* c, int ch, GwSiSet* out, uint32_t* occ_lookups) {
-    bool hasF = (c->si_kind == GW_SI_F || c->si_kind == GW_SI_BD) && ((c->f_valid >> ch) & 1);
-    bool hasB = (c->si_kind == GW_SI_B || c->si_kind == GW_SI_BD) && ((c->b_valid >> ch) & 1);
-    if (gw_dir(c) == GW_DIR_BF && c->cursor >= c->end - 1) hasF = false;
-    const int strand = gw_strand(c);
-    out->f_valid = out->b_valid = 0;
-    for (int i = 0; i < 4; ++i) { out->sif[i][0] = out->sif[i][1] = 0; out->sib[i][0] = out->sib[i][1] = 0; }
-    if (!hasF && !hasB) { out->kind = GW_SI_EMPTY; return; }
-    const int fm = hasF ? (strand == 0 ? 1 : 0) : (strand == 0 ? 0 : 1);
-    uint32_t f_lb = 0, f_ub = 0, b_lb = 0, b_ub = 0;   // intervals of `ch`, selected without indexing by a run-time value
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-        if (i == ch) { f_lb = c->sif[i][0]; f_ub = c->sif[i][1]; b_lb = c->sib[i][0]; b_ub = c->sib[i][1]; }
-    const uint32_t lb = gw_clampN(ix, hasF ? f_lb : b_lb);
-    const uint32_t ub = gw_clampN(ix, hasF ? f_ub : b_ub);
-    uint32_t lo[4], hi[4];
-    // both 64 B lines are requested before the first use, so that their misses overlap (the same line twice is one L1 miss)
-    const GwBlk bl = gw_load_block(ix.occ[fm] + (lb >> 7));
-    const GwBlk bu = gw_load_block(ix.occ[fm] + (ub >> 7));
-    gw_rank4(bl, lb & 127u, lo);
-    gw_rank4(bu, ub & 127u, hi);
-    *occ_lookups += 2;
-    uint8_t valid = 0;
-    uint32_t x = 0;
-    const uint32_t blb = b_lb;
-    for (int i = 0; i < 4; ++i) {
-        const uint32_t l = ix.C[fm][i] + lo[i], u = ix.C[fm][i] + hi[i];
-        if (hasF) { out->sif[i][0] = l; out->sif[i][1] = u; } else { out->sib[i][0] = l; out->sib[i][1] = u; }
-        if (l < u) valid |= (uint8_t)(1 << i);
-        if (hasF && hasB) {
-            const uint32_t y = hi[i] - lo[i];
-            out->sib[i][0] = blb + x; out->sib[i][1] = blb + x + y;
-            x += y;
-        }
-    }
-    if (hasF) {
-        out->f_valid = valid;
-        if (hasB) { out->b_valid = valid; out->kind = GW_SI_BD; } else out->kind = GW_SI_F;
-    } else {
-        out->b_valid = valid;
-        out->kind = GW_SI_B;
-    }
+#define GW_MID_TRY 1
+#define GW_MID_SPLIT 2
+#define GW_MID_REPORT 3
+
+template <int MAXH>
+GW_HD void gw_lane_reload(const GwSlab& s, GwLane<MAXH>& ln) {
+    const GwReadCtx* c = s.ctx();
+    ln.min_mm = c->min_mm; ln.best_score = c->best_score;
+    ln.n_fm = c->n_fm; ln.n_cut = c->n_cut; ln.n_filt = c->n_filt;
+    ln.qn = c->qn; ln.top = c->top; ln.free1 = c->free1;
+    const GwQEntry r = s.queue()[0];
+    ln.root_key = r.key; ln.root_off = r.off;
+}
+template <int MAXH>
+GW_HD void gw_lane_load(const GwSlab& s, GwLane<MAXH>& ln) {
+    const GwReadCtx* c = s.ctx();
+    ln.m = c->m; ln.k = c->k;
+    ln.sf_mm = -2; ln.sf_off = -1;
+    ln.base = ln.c_off = ln.cached = -1;
+    ln.mid = 0;
+    gw_lane_reload(s, ln);
+}
+template <int MAXH>
+GW_HD void gw_lane_flush(const GwSlab& s, const GwLane<MAXH>& ln) {
+    GwReadCtx* c = s.ctx();
+    c->n_fm = ln.n_fm; c->n_cut = ln.n_cut; c->n_filt = ln.n_filt;
+    c->qn = ln.qn; c->top = ln.top; c->free1 = ln.free1;
+    if (ln.qn > 0) { GwQEntry r; r.key = ln.root_key; r.off = ln.root_off; r.pad_ = 0; s.queue()[0] = r; }
 }
 
-// ReadAlignmentNFA.nextState + SearchState.nextState on a register copy `c` of the current state (rows in `prev`):
-// returns the arena offset of the new state, -1 for "no match" (null), -2 on slab overflow
-// MAXH: compile-time bound of the NFA height (k + 1). For MAXH <= 8 the rows are kept in registers (every loop over rows is
-// unrolled with constant indices); the generic form (MAXH == GW_MAX_ROWS) keeps them in local memory.
-template <int MAXH = GW_MAX_ROWS>
-GW_HD int32_t gw_next_state(const GwSlab& s, const GwState& c, const u64* prev, int ch, const GwSiSet& nextSi,
-                            const u64* sf_tbl, int sf_kk, GwState* built) {
-    GwReadCtx* ctx = s.ctx();
-    const int m_read = ctx->m;
-    const int height = c.height;
-    const int kOffset = c.k_offset;
-    const int k = kOffset + height - 1;
-    const int kr = k - kOffset;
-    const u64 qeq = gw_pattern_mask64(ctx, gw_strand(&c), m_read, gw_is_fwd(&c), gw_next_index(&c), c.pivot, c.cursor, ch, kr);
-    const int progressIndex = gw_processed(&c);
-    const int fragmentLength = gw_frag_len(&c);
-    u64 next[MAXH];
-    int minKwithMatch = k + 1, minKwithProgress = k + 1;
-    next[0] = (prev[0] & qeq) << 1;
-    if (next[0] != 0) { minKwithMatch = 0; minKwithProgress = 0; }
-    next[0] &= gw_staircase64(sf_tbl, m_read, sf_kk, kOffset, progressIndex - k);
-    const int mPos = k + fragmentLength - progressIndex;
-    int remove = -1;
-    bool hasMatch = false;
+// the state at `off` into the lane's registers
+template <int MAXH>
+GW_HD void gw_lane_fetch(const GwSlab& s, GwLane<MAXH>& ln, int32_t off) {
+    GwState* p = gw_st(s, off);
+    ln.C = *p;
+    const u64* rows = gw_rows(p);
     if constexpr (MAXH <= 8) {
 #pragma unroll
-        for (int i = 1; i < MAXH; ++i) {
-            if (i < height) {
-                u64 v = (prev[i] & qeq) << 1;
-                if (minKwithMatch > k && v != 0) minKwithMatch = i;
-                v |= prev[i - 1] | (prev[i - 1] << 1) | (next[i - 1] << 1);
-                v &= gw_staircase64(sf_tbl, m_read, sf_kk, kOffset + i, progressIndex - k);
-                if (minKwithProgress > k && (v & jshl(1ULL, height)) != 0) minKwithProgress = i;
-                next[i] = v;
-            } else next[i] = 0ULL;
-        }
-        if (mPos < 64) {
-#pragma unroll
-            for (int nm = 0; nm < MAXH; ++nm)
-                if (nm < height && remove < 0 && (next[nm] & jshl(1ULL, mPos)) != 0) { remove = nm; hasMatch = true; }
-        }
+        for (int i = 0; i < MAXH; ++i) ln.rows[i] = i < ln.C.height ? rows[i] : 0ULL;
     } else {
-#pragma unroll 1
-        for (int i = 1; i < height; ++i) {
-            u64 v = (prev[i] & qeq) << 1;
-            if (minKwithMatch > k && v != 0) minKwithMatch = i;
-            v |= prev[i - 1] | (prev[i - 1] << 1) | (next[i - 1] << 1);
-            v &= gw_staircase64(sf_tbl, m_read, sf_kk, kOffset + i, progressIndex - k);
-            if (minKwithProgress > k && (v & jshl(1ULL, height)) != 0) minKwithProgress = i;
-            next[i] = v;
+        for (int i = 0; i < ln.C.height; ++i) ln.rows[i] = rows[i];
+    }
+    ln.cached = off;
+}
+
+// java.util.PriorityQueue.offer / poll as above, with entry 0 in the lane's registers
+template <int MAXH>
+GW_HD bool gw_lq_add(const GwSlab& s, GwLane<MAXH>& ln, int32_t e, const u64 ke) {
+    GwQEntry* q = s.queue();
+    int k = ln.qn;
+    if ((uint32_t)k >= s.sp.queue_cap) return false;
+    ln.qn = k + 1;
+    while (k > 2) {
+        const int parent = (k - 1) >> 1;
+        const GwQEntry p = q[parent];
+        if (ke >= p.key) break;
+        q[k] = p;
+        k = parent;
+    }
+    if (k > 0 && k <= 2 && ke < ln.root_key) {   // the parent is the root
+        GwQEntry p; p.key = ln.root_key; p.off = ln.root_off; p.pad_ = 0;
+        q[k] = p;
+        k = 0;
+    }
+    if (k == 0) { ln.root_key = ke; ln.root_off = e; }
+    else { GwQEntry n; n.key = ke; n.off = e; n.pad_ = 0; q[k] = n; }
+    return true;
+}
+template <int MAXH>
+GW_HD int32_t gw_lq_poll(const GwSlab& s, GwLane<MAXH>& ln) {
+    GwQEntry* q = s.queue();
+    const int n = --ln.qn;
+    const int32_t result = ln.root_off;
+    if (n != 0) {
+        const GwQEntry x = q[n];
+        int k = 0;
+        const int half = n >> 1;
+        while (k < half) {
+            int child = (k << 1) + 1;
+            const int right = child + 1;
+            GwQEntry cc = q[child];
+            if (right < n) { const GwQEntry cr = q[right]; if (cc.key > cr.key) { cc = cr; child = right; } }
+            if (x.key <= cc.key) break;
+            if (k == 0) { ln.root_key = cc.key; ln.root_off = cc.off; } else q[k] = cc;
+            k = child;
         }
-        if (mPos < 64) {
-            for (int nm = 0; nm < height; ++nm)
-                if ((next[nm] & jshl(1ULL, mPos)) != 0) { remove = nm; hasMatch = true; break; }
-        }
+        if (k == 0) { ln.root_key = x.key; ln.root_off = x.off; } else q[k] = x;
     }
-    if (remove < 0) {
-        int minK = minKwithMatch < minKwithProgress ? minKwithMatch : minKwithProgress;
-        if (minK < k) remove = minK;
-        else return -1;
-    }
-    const int newHeight = height - remove;
-    int32_t off = gw_alloc_state(s, newHeight);
-    if (off < 0) return -2;
-    GwState n;
-    // Cursor.next
-    int nextCursor = c.cursor, d = gw_dir(&c);
-    if (d == GW_DIR_F) ++nextCursor;
-    else if (d == GW_DIR_B) --nextCursor;
-    else if (nextCursor + 1 < c.end) ++nextCursor;
-    else { d = GW_DIR_B; nextCursor = c.pivot; }
-    n.start = c.start; n.end = c.end; n.cursor = (int16_t)nextCursor; n.pivot = c.pivot;
-    n.cflag = (uint8_t)(gw_strand(&c) | (d << 1));
-    // currentSi = nextCursor.isForwardSearch ? siTable.getForward(ch) : siTable.getBackward(ch)
-    const bool fwd = d != GW_DIR_B;
-    const bool has = fwd ? ((c.si_kind == GW_SI_F || c.si_kind == GW_SI_BD) && ((c.f_valid >> ch) & 1))
-                         : ((c.si_kind == GW_SI_B || c.si_kind == GW_SI_BD) && ((c.b_valid >> ch) & 1));
-    uint32_t clb = 0, cub = 0;   // selected without indexing the interval tables by a run-time value
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-        if (i == ch) { clb = fwd ? c.sif[i][0] : c.sib[i][0]; cub = fwd ? c.sif[i][1] : c.sib[i][1]; }
-    n.has_cur = has ? 1 : 0;
-    n.cur_lb = has ? clb : 0;
-    n.cur_ub = has ? cub : 0;
-    n.si_kind = nextSi.kind; n.f_valid = nextSi.f_valid; n.b_valid = nextSi.b_valid;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        n.sif[i][0] = nextSi.sif[i][0]; n.sif[i][1] = nextSi.sif[i][1];
-        n.sib[i][0] = nextSi.sib[i][0]; n.sib[i][1] = nextSi.sib[i][1];
-    }
-    n.height = (uint8_t)newHeight; n.k_offset = (uint8_t)(kOffset + remove); n.has_nfa = 1;
-    n.state = gw_pack_state(ch, kOffset + remove, gw_priority(&c), hasMatch);
-    n.next_split = c.next_split;
-    *gw_st(s, off) = n;
-    *built = n;
-    u64* nr = gw_rows(gw_st(s, off));
-    if constexpr (MAXH <= 8) {
-        // remove == 0 keeps the OLD automaton (sic, ReadAlignmentNFA.java:206-207)
-#pragma unroll
-        for (int j = 0; j < MAXH; ++j)
-            if (j >= remove && j < height) nr[j - remove] = remove == 0 ? prev[j] : (next[j] >> 1);
-    } else {
-        if (remove == 0) { for (int h = 0; h < newHeight; ++h) nr[h] = prev[h]; }  // sic: the OLD automaton (ReadAlignmentNFA.java:206-207)
-        else { for (int h = 0; h < newHeight; ++h) nr[h] = next[h + remove] >> 1; }
-    }
-    return off;
+    return result;
+}
+
+// a slot for a new state: the recycled one if there is one, else from the arena; -1 on overflow
+template <int MAXH>
+GW_HD int32_t gw_lane_alloc_state(const GwSlab& s, GwLane<MAXH>& ln) {
+    if (ln.free1 >= 0) { const int32_t o = ln.free1; ln.free1 = -1; return o; }
+    const uint32_t words = gw_state_words(ln.k), top = (uint32_t)ln.top;
+    if (top + words > s.sp.slab_words) return -1;
+    ln.top = (int32_t)(top + words);
+    return (int32_t)top;
+}
+// the polled state of a finished step that heads no split chain is unreachable: its slot goes to the next state built
+template <int MAXH>
+GW_HD void gw_lane_free_state(GwLane<MAXH>& ln, int32_t off) {
+    if (ln.free1 < 0) ln.free1 = off;
+    if (ln.cached == off) ln.cached = -1;
+}
+
+GW_HD int gw_q_symbol(const GwReadCtx* c, int strand, int i) {
+    return (int)((((c->qhi[strand][i >> 6] >> (i & 63)) & 1ULL) << 1) | ((c->qlo[strand][i >> 6] >> (i & 63)) & 1ULL));
 }
 
 // SearchState.nextStateAfterSplit (clip == false) / nextStateAfterClipping (clip == true) on a register copy of the current

@@ -25,12 +25,10 @@ struct GwPendFrag {
     uint32_t cig[GW_CIG_CAP];
 };
 
-// locate + verification of one pending fragment, resumable (fused kernel, gw_fused.cuh)
+// verification of one pending fragment (gw_job.cuh): lives in the local memory of the lane that runs it
 #define GW_RW_WORDS ((GW_MAX_WINDOW + 63) / 64)
 struct GwJob {
     int32_t frag;            // index into pend[]
-    int32_t lf_j;            // LF steps done so far
-    uint32_t lf_cursor;      // current SA row of the walk
     int32_t pad_;
     GwDp dp;
     u64 peq[4][GW_MAX_NB];   // pattern masks of the query fragment
@@ -45,6 +43,7 @@ struct GwReadCtx {
     int32_t n_fm, n_sw, n_cut, n_filt;
     int32_t qn, top, phase, status;
     int32_t n_hits;
+    int32_t free1;            // one recycled state slot (arena offset) or -1: see gw_state_words
     int32_t scan_mm[2], scan_ls[2], scan_le[2];
     uint32_t scan_lb[2], scan_ub[2];
     int32_t pend_base, pend_n;
@@ -53,7 +52,6 @@ struct GwReadCtx {
     GwSlabParams sp;          // geometry of the slab this context lives in
     uint32_t occ_scan, occ_search, occ_locate;   // occurrence-table lookups done for this read (roofline work unit)
     GwPendFrag pend[2];
-    GwJob job;
     u64 qlo[2][GW_MAX_NB], qhi[2][GW_MAX_NB];  // q[0] = read, q[1] = its complement, N replaced by A in both
 };
 
@@ -147,6 +145,13 @@ struct GwHitNode {
 #define GW_HIT_WORDS ((uint32_t)((sizeof(GwHitNode) + 7) / 8))
 GW_HD uint32_t* gw_hit_cigar(GwHitNode* h) { return reinterpret_cast<uint32_t*>(reinterpret_cast<u64*>(h) + GW_HIT_WORDS); }
 
+// Every search state of a read is allocated with room for the full NFA height of the read (k + 1 rows), whatever its own height:
+// states then have ONE size per read, so the slot of a state that can no longer be reached (the polled state of a finished step
+// that heads no split chain: nothing but its queue entry ever referred to it) can be handed to the next state that is built.
+// The usual step — extension with the read's own base — even rebuilds the child in the parent's slot, so a read that follows its
+// greedy path keeps rewriting the same 128 bytes instead of walking through the arena.
+GW_HD uint32_t gw_state_words(int k) { return (GW_STATE_WORDS + (uint32_t)k + 2u) & ~1u; }
+
 // bump allocation; returns -1 (and the caller flags the read for the large-slab pass) on overflow
 GW_HD int32_t gw_alloc(const GwSlab& s, uint32_t words) {
     GwReadCtx* c = s.ctx();
@@ -163,12 +168,13 @@ GW_HD int32_t gw_alloc(const GwSlab& s, uint32_t words) {
 // (no pointer into the old area is live then), when the free space falls below what one step can allocate at most:
 // up to 5 candidate states + 4 states of the split / clip children + 2 hit nodes.
 GW_HD uint32_t gw_step_alloc_bound(int k) {
-    const uint32_t st = (GW_STATE_WORDS + (uint32_t)k + 2u) & ~1u;
-    return 9u * st + 2u * ((GW_HIT_WORDS + GW_CIG_CAP / 2u + 1u) & ~1u);
+    return 9u * gw_state_words(k) + 2u * ((GW_HIT_WORDS + GW_CIG_CAP / 2u + 1u) & ~1u);
 }
-GW_HD bool gw_wants_promotion(const GwSlab& s) {
+// `top`: the read's allocation cursor (kept in a register by the search lanes)
+GW_HD bool gw_wants_promotion(const GwSlab& s, uint32_t top, int k) {
+    if (top + gw_step_alloc_bound(k) <= s.sp.slab_words) return false;
     const GwReadCtx* c = s.ctx();
-    return (uint32_t)c->top + gw_step_alloc_bound(c->k) > s.sp.slab_words && c->ext_pool != nullptr && c->ext == nullptr;
+    return c->ext_pool != nullptr && c->ext == nullptr;
 }
 // the move in three parts, so that the copy can be shared by the lanes of a warp: take a block from the pool (null: none left) ...
 GW_COLD u64* gw_promote_take(const GwSlab& s) {
@@ -204,65 +210,57 @@ GW_COLD bool gw_promote(GwSlab& s, u64** slab_ptr) {
     return true;
 }
 
-// ---- BitVector.substring64 over nb blocks -----------------------------------------------------------------
-GW_HD u64 gw_substring64(const u64* block, int nb, int start, int end) {
-    int pos = start / 64;
-    if (pos >= nb) return 0ULL;
-    int range = end - start;
-    u64 mask = (range >= 64) ? ~0ULL : ~jshl(~0ULL, range);
-    int offset = start % 64;
-    u64 low = jushr(block[pos], offset);
-    u64 high = (pos + 1 < nb) ? jshl(block[pos + 1] & ~jshl(~0ULL, offset), 64 - offset) : 0ULL;
-    return (high | low) & mask;
+// ---- bit-vector windows ------------------------------------------------------------------------------------
+// All of these are written without data-dependent branches (clamped indices + selects): they sit in the hottest loop of the
+// search lanes, where a branch costs both divergence and instruction-cache footprint.
+
+// (hi:lo) >> off for off in 0..63, as BitVector.substring64 combines two blocks (BitVector.java:106-116)
+GW_HD u64 gw_funnel64(u64 lo, u64 hi, int off) { return (lo >> off) | ((hi << 1) << (63 - off)); }
+
+// BitVector.substring64(start, start + 64) over nb blocks, start >= 0
+GW_HD u64 gw_substring64(const u64* block, int nb, int start) {
+    const int pos = start >> 6, off = start & 63;
+    const u64 lo = block[gw_min(pos, nb - 1)], hi = block[gw_min(pos + 1, nb - 1)];
+    return gw_funnel64(pos < nb ? lo : 0ULL, pos + 1 < nb ? hi : 0ULL, off);
 }
 
 // QueryMask pattern vectors are not materialised: bit i of patternMaskF[ch] is (q[i] == ch), which is read straight from the
 // 2-bit planes of the read, and patternMaskR is patternMaskF mirrored (bit m-1-i), i.e. a bit reversal of a forward window.
-// 64 bits of patternMaskF[ch] starting at bit `start` (bits outside [0, m) are zero)
+// One 64-symbol word of patternMaskF[ch] (bits at positions >= m are zero; w outside [0, nb) gives zero)
+GW_HD u64 gw_match_word(const u64* qlo, const u64* qhi, int m, int nb, int ch, int w) {
+    const int wi = gw_min(gw_max(w, 0), nb - 1);
+    const u64 lo = qlo[wi], hi = qhi[wi];
+    const int rem = m - (wi << 6);
+    const u64 valid = rem >= 64 ? ~0ULL : ((1ULL << rem) - 1ULL);
+    const u64 f = ((ch & 2) ? hi : ~hi) & ((ch & 1) ? lo : ~lo) & valid;
+    return w == wi ? f : 0ULL;
+}
+// 64 bits of patternMaskF[ch] starting at bit `start` (any integer; bits outside [0, m) are zero)
 GW_HD u64 gw_match_window(const u64* qlo, const u64* qhi, int m, int ch, int start) {
     const int nb = (m + 63) >> 6;
-    int lsh = 0;
-    if (start < 0) {
-        if (start <= -64) return 0ULL;
-        lsh = -start; start = 0;
-    }
-    const int w = start >> 6, off = start & 63;
-    if (w >= nb) return 0ULL;
-    u64 f0, f1 = 0ULL;
-    {
-        const u64 lo = qlo[w], hi = qhi[w];
-        const u64 valid = (w == nb - 1 && (m & 63)) ? ((1ULL << (m & 63)) - 1ULL) : ~0ULL;
-        f0 = ((ch & 2) ? hi : ~hi) & ((ch & 1) ? lo : ~lo) & valid;
-    }
-    if (off != 0 && w + 1 < nb) {
-        const u64 lo = qlo[w + 1], hi = qhi[w + 1];
-        const u64 valid = (w + 1 == nb - 1 && (m & 63)) ? ((1ULL << (m & 63)) - 1ULL) : ~0ULL;
-        f1 = ((ch & 2) ? hi : ~hi) & ((ch & 1) ? lo : ~lo) & valid;
-    }
-    u64 v = off ? ((f0 >> off) | (f1 << (64 - off))) : f0;
-    return v << lsh;
+    if (start <= -64) return 0ULL;
+    const int w = start >> 6, off = start & 63;   // arithmetic shift: w == -1 for start in [-63, -1]
+    return gw_funnel64(gw_match_word(qlo, qhi, m, nb, ch, w), gw_match_word(qlo, qhi, m, nb, ch, w + 1), off);
 }
 
 // QueryMask.getBidirectionalPatternMask64 (QueryMask.java:73-97) on the planes of q[strand]
 GW_HD u64 gw_pattern_mask64(const GwReadCtx* c, int strand, int m, bool dirIsForward, int nextIdx, int pivot, int cursor, int ch, int margin) {
     const u64* qlo = c->qlo[strand];
     const u64* qhi = c->qhi[strand];
-    if (dirIsForward) {
-        const int pos = nextIdx - margin;
-        if (pos < 0) return jshl(gw_match_window(qlo, qhi, m, ch, 0), -pos);   // substring64(0, 64) << -pos
-        return gw_match_window(qlo, qhi, m, ch, pos);                          // substring64(pos, m): bits >= m are already zero
-    }
-    // patternMaskR.substring64(m - pivot, m - pivot + 64): bit j = F[pivot - 1 - j]
-    u64 p = gw_brev64(gw_match_window(qlo, qhi, m, ch, pivot - 64));
-    const int rshift = pivot - cursor - margin;
-    return rshift >= 0 ? jushr(p, rshift) : jshl(p, -rshift);
+    // forward: substring64(pos, m) with pos = nextIdx - margin, or substring64(0, 64) << -pos for negative pos (the bits shifted in
+    // from below position 0 are zero either way). backward: patternMaskR.substring64(m - pivot, m - pivot + 64), whose bit j is
+    // F[pivot - 1 - j], shifted by pivot - cursor - margin (right if positive)
+    const u64 win = gw_match_window(qlo, qhi, m, ch, dirIsForward ? gw_max(nextIdx - margin, 0) : pivot - 64);
+    const int sh = dirIsForward ? gw_min(nextIdx - margin, 0) : pivot - cursor - margin;
+    const u64 p = dirIsForward ? win : gw_brev64(win);
+    return sh >= 0 ? jushr(p, sh) : jshl(p, -sh);
 }
 
 // StaircaseFilter.getStairCaseMask64bit for the filter (m, kk); tbl points at the (kk+1) x nb words of that filter
 GW_HD u64 gw_staircase64(const u64* tbl, int m, int kk, int row, int offset) {
-    if (row >= kk + 1) return 0ULL;
     const int nb = (m + 63) >> 6;
-    const u64* bv = tbl + row * nb;
-    if (offset >= 0) return jshl(~0ULL, m - offset) | gw_substring64(bv, nb, offset, offset + 64);
-    return jshl(gw_substring64(bv, nb, 0, 64), -offset);
+    const u64* bv = tbl + gw_min(row, kk) * nb;
+    const u64 sub = gw_substring64(bv, nb, gw_max(offset, 0));
+    const u64 v = offset >= 0 ? (jshl(~0ULL, m - offset) | sub) : jshl(sub, -offset);
+    return row >= kk + 1 ? 0ULL : v;
 }

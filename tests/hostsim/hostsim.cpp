@@ -8,10 +8,11 @@
 #include <string.h>
 
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/gw_align.h"
-#include "../../genome_weaver_align_b200/csrc/gw_fused.cuh"
+#include "../../genome_weaver_align_b200/csrc/gw_job.cuh"
 #include "../../genome_weaver_align_b200/csrc/gw_host.h"
 #include "../../genome_weaver_align_b200/csrc/gw_image.h"
 
@@ -102,87 +103,56 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
 
         std::vector<std::vector<u64>> slab_store(n_reads);
         std::vector<u64*> slabs(n_reads, nullptr);
-        std::vector<uint32_t> act[2], loc(2 * (size_t)n_reads + 2), ver(2 * (size_t)n_reads + 2);
-        act[0].resize(n_reads + 1); act[1].resize(n_reads + 1);
-        uint32_t ctr[4];
-        const uint32_t step_budget = getenv("GWSIM_STEP_BUDGET") ? (uint32_t)atoi(getenv("GWSIM_STEP_BUDGET")) : 0;
         uint32_t max_m = 1;
         for (uint32_t i = 0; i < n_reads; ++i) max_m = std::max<uint32_t>(max_m, (uint32_t)std::min<uint64_t>(offsets[i + 1] - offsets[i], GW_MAX_READ_LEN));
         std::vector<GwU64x2> hist((size_t)(max_m + 2 * kmax + 2) * ((max_m + 63) / 64), GwU64x2{0xDEADBEEFDEADBEEFULL, 0xFEEDFACEFEEDFACEULL});   // poison
-
-        const bool fused = !(getenv("GWSIM_ROUNDS") && atoi(getenv("GWSIM_ROUNDS")));
-        GwFusedParams fp;
-        fp.q_lf = getenv("GWSIM_Q_LF") ? atoi(getenv("GWSIM_Q_LF")) : 4;
-        fp.stick = 32;
-        fp.q_cols = getenv("GWSIM_Q_COLS") ? atoi(getenv("GWSIM_Q_COLS")) : 8;
-        auto rounds = [&](std::vector<uint32_t> cur) {
-            if (fused) {   // like the fused kernel: every read is driven to completion by one lane, tick by tick
-                for (uint32_t slot : cur) {
-                    GwSlab s(slabs[slot]);
-                    GwSearchLane L;
-                    L.base = L.c_off = -1; L.mid = 0;
-                    int lp = gw_fused_start(env, s, slot);
-                    while (lp != GW_LP_FETCH) lp = gw_fused_tick(lp, env, s, slot, L, fp, hist.data(), 1);
-                }
-                return;
+        // GWSIM_NOCACHE=1: the lane re-reads its state from the work area before every slice; GWSIM_SPILL=n: the lane is written back
+        // and re-read every n slices (as the flow kernel does around its out-of-line continuations). Neither may change any result.
+        const bool nocache = getenv("GWSIM_NOCACHE") && atoi(getenv("GWSIM_NOCACHE"));
+        const int spill = getenv("GWSIM_SPILL") ? atoi(getenv("GWSIM_SPILL")) : 0;
+        auto verify_pending = [&](const GwSlab& s) {   // what a verification batch of the flow kernel does for one parked read
+            GwReadCtx* c = s.ctx();
+            for (int f = 0; f < c->pend_n; ++f) {
+                if (c->pend[f].kind != 2) continue;
+                uint32_t steps = 0;
+                c->pend[f].textpos = gw_sa_get(env.ix, c->pend[f].fm, c->pend[f].sa_index, &steps);
+                c->occ_locate += steps;
             }
-            if (getenv("GWSIM_ROUNDS") && atoi(getenv("GWSIM_ROUNDS")) == 2) {   // like the pool kernel: S / L / D phases over a pool of reads
-                const uint32_t bud = step_budget ? step_budget : 32;
-                while (!cur.empty()) {
-                    std::vector<uint32_t> next, fr;
-                    for (uint32_t slot : cur) {
-                        GwSlab s(slabs[slot]);
-                        GwSearchLane L;
-                        L.base = L.c_off = -1; L.mid = 0;
-                        int r = gw_resume_read(env, s, slot, gw_no_queues());
-                        uint32_t budget = bud;
-                        while (r == GW_STEP_CONTINUE) {
-                            if (!L.mid) r = gw_search_poll(env, s, slot, gw_no_queues(), L);
-                            if (r == GW_STEP_CONTINUE && L.mid) r = gw_search_try(env, s, L);
-                            if (r == GW_STEP_CONTINUE) {
-                                if (--budget == 0 && !L.mid) { next.push_back(slot); break; }
-                                else if (budget == 0) budget = 1;
-                            }
-                        }
-                        if (r == GW_STEP_PARKED) {
-                            next.push_back(slot);
-                            for (int f = 0; f < s.ctx()->pend_n; ++f) if (s.ctx()->pend[f].kind == 2) fr.push_back(slot * 2u + (uint32_t)f);
-                        }
-                    }
-                    for (uint32_t id : fr) {
-                        GwReadCtx* c = reinterpret_cast<GwReadCtx*>(slabs[id >> 1]);
-                        uint32_t steps = 0;
-                        c->pend[id & 1u].textpos = gw_sa_get(env.ix, c->pend[id & 1u].fm, c->pend[id & 1u].sa_index, &steps);
-                        c->occ_locate += steps;
-                    }
-                    for (uint32_t id : fr) {
-                        GwSlab s(slabs[id >> 1]);
-                        if (s.ctx()->phase == GW_PH_WAIT_EXACT) continue;
-                        GwJob job;
-                        gw_verify_frag(env, s, &job, (int)(id & 1u), hist.data(), 1);
-                    }
-                    cur.swap(next);
-                }
-                return;
+            if (c->phase == GW_PH_WAIT_EXACT) return;
+            for (int f = 0; f < c->pend_n; ++f) {
+                if (c->pend[f].kind != 2) continue;
+                GwJob job;
+                gw_verify_frag(env, s, &job, f, hist.data(), 1);
             }
-            int flip = 0;
-            while (!cur.empty()) {
-                memset(ctr, 0, sizeof(ctr));
-                GwRoundQueues rq;
-                rq.next_active = act[flip].data(); rq.locate_req = loc.data(); rq.verify_req = ver.data(); rq.counters = ctr;
-                for (uint32_t slot : cur) {   // like the search kernel: resume, then steps; a step budget emulates the tail yield
-                    GwSlab s(slabs[slot]);
-                    int r = gw_resume_read(env, s, slot, rq);
-                    uint32_t budget = step_budget;
-                    while (r == GW_STEP_CONTINUE) {
-                        r = gw_step_read(env, s, slot, rq);
-                        if (r == GW_STEP_CONTINUE && step_budget && --budget == 0) { gw_yield_read(s, slot, rq); break; }
-                    }
+        };
+        auto drive = [&](uint32_t slot, auto maxh_tag) {   // like one lane of the flow kernel: the read is driven to completion slice by slice
+            constexpr int MAXH = decltype(maxh_tag)::value;
+            GwSlab s(slabs[slot]);
+            for (;;) {
+                int r = gw_resume_read(env, s);
+                if (r == GW_STEP_DONE) return;
+                if (r == GW_STEP_PARKED) { verify_pending(s); continue; }
+                GwLane<MAXH> ln;
+                gw_lane_load(s, ln);
+                int slices = 0;
+                while (r == GW_STEP_CONTINUE) {
+                    if (nocache && ln.mid == 0) ln.cached = -1;
+                    if (spill && ++slices % spill == 0) { gw_lane_flush(s, ln); gw_lane_reload(s, ln); }
+                    if (ln.mid == 0) r = gw_lane_poll(env, s, ln);
+                    if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY) r = gw_lane_try(env, s, ln);
+                    if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_SPLIT) r = gw_lane_split(env, s, ln);
+                    if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_REPORT) r = gw_lane_report(env, s, ln);
                 }
-                for (uint32_t i = 0; i < ctr[1]; ++i) gw_locate_req(env.ix, slabs[loc[i] >> 1], loc[i] & 1u);
-                for (uint32_t i = 0; i < ctr[2]; ++i) gw_verify_req(env.ix, slabs[ver[i] >> 1], ver[i] & 1u, env.cfg.band_width, hist.data(), 1);
-                cur.assign(act[flip].begin(), act[flip].begin() + ctr[0]);
-                flip ^= 1;
+                gw_lane_flush(s, ln);
+                if (r == GW_STEP_DONE) return;
+                verify_pending(s);
+            }
+        };
+        auto rounds = [&](const std::vector<uint32_t>& cur) {
+            for (uint32_t slot : cur) {
+                if (kmax + 1 <= 4) drive(slot, std::integral_constant<int, 4>());
+                else if (kmax + 1 <= 8) drive(slot, std::integral_constant<int, 8>());
+                else drive(slot, std::integral_constant<int, GW_MAX_ROWS>());
             }
         };
         auto pass = [&](const std::vector<uint32_t>& slots, uint32_t words_per_slab) {

@@ -203,11 +203,11 @@ def test_sam_parity_large_work_areas_in_chunks(small):
     # outcomes are written back to the small work areas between chunks
     reads = synth.simulate_reads(small["g"], 1500, 100, 3, 79)
     compare(small["idx"], small["oidx"], reads, gw.AlignmentConfig(k=3), dict(k=3), slab_words=1024, tier_budget_mb=1)
-    compare(small["idx"], small["oidx"], reads, gw.AlignmentConfig(k=3), dict(k=3), slab_words=768, tier_budget_mb=1, fused=3)
+    compare(small["idx"], small["oidx"], reads, gw.AlignmentConfig(k=3), dict(k=3), slab_words=768, tier_budget_mb=1, ext_pct=0)
 
 
-@pytest.mark.parametrize("opts", [dict(slab_words=1024, ext_mult=2), dict(slab_words=1024, ext_pct=1, ext_mult=7), dict(slab_words=768, ext_mult=1, fused=3),
-                                  dict(slab_words=1024, ext_pct=0), dict(slab_words=1024, ext_mult=3, fused=0), dict(slab_words=1024, ext_mult=3, fused=1)])
+@pytest.mark.parametrize("opts", [dict(slab_words=1024, ext_mult=2), dict(slab_words=1024, ext_pct=1, ext_mult=7), dict(slab_words=768, ext_mult=1),
+                                  dict(slab_words=1024, ext_pct=0), dict(slab_words=1024, ext_mult=3)])
 def test_sam_parity_moves_to_larger_work_areas(small, opts):
     # a read whose work area is nearly full is moved into a larger block taken from a pool and goes on there; when the pool is empty,
     # the block fills up too or the queue overflows, the read is run again from the start with a larger work area: the outcome must
@@ -216,13 +216,11 @@ def test_sam_parity_moves_to_larger_work_areas(small, opts):
     compare(small["idx"], small["oidx"], reads, gw.AlignmentConfig(k=3), dict(k=3), **opts)
 
 
-@pytest.mark.parametrize("opts", [dict(fused=0), dict(fused=0, tail_steps=3), dict(fused=1, q_lf=1, q_cols=1), dict(fused=1, q_lf=7, q_cols=33),
-                                  dict(fused=2, pool_budget=3, pool_tail=0), dict(fused=2, pool_tail=1024), dict(fused=2, pool_budget=1000, pool_blocks=1), dict(fused=2),
-                                  dict(fused=3, flow_batch=1, flow_age=1), dict(fused=3, flow_batch=32, flow_age=1000, flow_flush=32),
-                                  dict(fused=3, flow_fetch=1, flow_flush=1, pool_blocks=3), dict(fused=3, pool_blocks=1)])
-def test_sam_parity_round_mode_and_slice_sizes(small, opts):
-    # the round-based kernels (search / locate / verify launched per round) and the fused lane program must agree with the oracle
-    # whatever the slice sizes are
+@pytest.mark.parametrize("opts", [dict(flow_batch=1, flow_age=1), dict(flow_batch=32, flow_age=1000, flow_flush=32),
+                                  dict(flow_fetch=1, flow_flush=1, flow_blocks=3), dict(flow_blocks=1), dict(flow_blocks=1000)])
+def test_sam_parity_flow_kernel_tunables(small, opts):
+    # how the warps of the flow kernel batch their work (deferred continuations, verification batches, grid size) must not change
+    # any result
     reads = synth.simulate_reads(small["g"], 1500, 100, 3, 78)
     compare(small["idx"], small["oidx"], reads, gw.AlignmentConfig(k=3), dict(k=3), **opts)
 

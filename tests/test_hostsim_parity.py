@@ -59,11 +59,15 @@ def test_abort_domain_and_small_slabs(rnd):
     assert rs["overflow_reads"] > 0   # the larger work-area tiers were exercised
 
 
-def test_yielding_rounds(rnd, monkeypatch):
-    # the search kernel lets a long-running read yield to the next round; results must not depend on where it yields
+@pytest.mark.parametrize("env", [dict(GWSIM_NOCACHE="1"), dict(GWSIM_SPILL="1"), dict(GWSIM_SPILL="5", GWSIM_NOCACHE="1")])
+def test_lane_register_copy_is_transparent(rnd, monkeypatch, env):
+    # a search lane keeps the read's counters, queue root and current state in registers; re-reading the state from the work area
+    # before every step, or writing the lane back and re-reading it between slices, must not change any result
     g, oi, si = rnd
-    monkeypatch.setenv("GWSIM_STEP_BUDGET", "7")
-    _compare(oi, si, synth.simulate_reads(g, 200, 100, 3, 13), k=3)
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    _compare(oi, si, synth.simulate_reads(g, 300, 100, 3, 13), k=3)
+    _compare(oi, si, synth.simulate_reads(g, 100, 150, 6, 14), k=6)
 
 
 def test_edge_reads(rnd):

@@ -21,28 +21,7 @@ for f,ln,ie,te,s,st in lines:
     byf[f][0]+=s; byf[f][1]+=ie; byf[f][2]+=te
 for f,(s,ie,te) in sorted(byf.items(), key=lambda x:-x[1][0]):
     print("%-28s smp %5.1f%% inst %5.1f%% thr/inst %.1f"%(f,100*s/tot_s,100*ie/tot_i,te/max(ie,1)))
-regions = {
- 'locate loop (kernels.cu 421-431)': [('gw_kernels.cu',421,431)],
- 'suffix_link+rank1+rankN (fm 56-92)': [('gw_fm.cuh',56,92)],
- 'rank4/halves/masks (fm 31-54)': [('gw_fm.cuh',31,54)],
- 'load_block (fm 13-18)': [('gw_fm.cuh',13,18)],
- 'dp columns (verify 45-130)': [('gw_verify.cuh',28,141)],
- 'traceback (verify 143-214)': [('gw_verify.cuh',142,223)],
- 'fused: begin_dp/job (fused 66-205)': [('gw_fused.cuh',1,230)],
- 'queue ops (search 43-110)': [('gw_search.cuh',43,110)],
- 'score/numsplit (search 24-42)': [('gw_search.cuh',24,42)],
- 'next_si (search 158-206)': [('gw_search.cuh',158,206)],
- 'next_state (search 208-314)': [('gw_search.cuh',208,314)],
- 'split/update/hits (search 316-430)': [('gw_search.cuh',315,430)],
- 'search_poll (automaton 227-265)': [('gw_automaton.cuh',227,265)],
- 'search_try (automaton 290-365)': [('gw_automaton.cuh',290,365)],
- 'resume/report (automaton 1-226)': [('gw_automaton.cuh',1,226)],
- 'search_split (automaton 267-288)': [('gw_automaton.cuh',266,289)],
- 'state.cuh accessors 114-136': [('gw_state.cuh',97,137)],
- 'state.cuh alloc/promote 150-205': [('gw_state.cuh',138,206)],
- 'state.cuh substring/match_window/pattern/staircase 207-268': [('gw_state.cuh',207,268)],
- 'kernels.cu flow loop': [('gw_kernels.cu',390,547)],
-}
+regions = {}   # optional: name -> [(file, first line, last line)]
 for name,rs in regions.items():
     s=ie=te=0; st=collections.Counter()
     for f,ln,i,t,sm,sd in lines:
