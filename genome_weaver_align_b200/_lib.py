@@ -39,6 +39,8 @@ SYMBOLS = {
     "gw_last_error": (C.c_char_p, []),
     "gw_index_build": (C.c_int, [C.c_char_p, C.c_int]),
     "gw_index_open": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(_P)]),
+    "gw_index_locate_table": (C.c_int, [_P, C.c_int]),
+    "gw_index_locate_step": (C.c_int, [_P]),
     "gw_index_from_sequence": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(_P)]),
     "gw_index_close": (None, [_P]),
     "gw_index_text_size": (C.c_int64, [_P]),

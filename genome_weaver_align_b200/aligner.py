@@ -65,6 +65,13 @@ class FMIndexOnGenome:
         L.check(L.lib().gw_index_from_sequence(name.encode(), seq.encode(), device, C.byref(h)))
         return cls(h)
 
+    def locateTable(self, step):
+        """suffix-array value of every step-th row in HBM (1, 2, 4, 8, 16; 32: the .ssa samples only; 0: automatic, as load() does)"""
+        L.check(L.lib().gw_index_locate_table(self._h, step))
+
+    def locateStep(self):
+        return L.lib().gw_index_locate_step(self._h)
+
     def textSize(self):
         return L.lib().gw_index_text_size(self._h)
 

@@ -86,9 +86,10 @@ struct gw_index {
     uint64_t N = 0;
     std::vector<GwContig> contigs;
     GwIndexView view;
+    DBuf loc[2];   // densified locate table (empty: the .ssa samples serve)
     DBuf occ[2], ssa[2], ref_lo, ref_hi, ref_nf, ctg_off, ctg_id, ctg_rank;
     ~gw_index() {
-        for (int s = 0; s < 2; ++s) { occ[s].release(); ssa[s].release(); }
+        for (int s = 0; s < 2; ++s) { occ[s].release(); ssa[s].release(); loc[s].release(); }
         ref_lo.release(); ref_hi.release(); ref_nf.release(); ctg_off.release(); ctg_id.release(); ctg_rank.release();
     }
 };
@@ -115,7 +116,9 @@ void make_device_index(gw_index* ix, const GwHostIndex& h, int device) {
         v.occ[s] = ix->occ[s].as<GwOccBlock>();
         upload(ix->ssa[s], h.ssa[s].data(), h.ssa[s].size() * sizeof(uint32_t));
         v.ssa[s] = ix->ssa[s].as<uint32_t>();
+        v.loc[s] = v.ssa[s];
     }
+    v.loc_step = GW_SSA_L;
     upload(ix->ref_lo, img.ref_lo.data(), img.ref_lo.size() * 8); upload(ix->ref_hi, img.ref_hi.data(), img.ref_hi.size() * 8);
     upload(ix->ref_nf, img.ref_nf.data(), img.ref_nf.size() * 8);
     v.ref_lo = ix->ref_lo.as<u64>(); v.ref_hi = ix->ref_hi.as<u64>(); v.ref_nf = ix->ref_nf.as<u64>();
@@ -123,6 +126,32 @@ void make_device_index(gw_index* ix, const GwHostIndex& h, int device) {
     upload(ix->ctg_rank, img.ctg_rank.data(), img.ctg_rank.size() * 4);
     v.ctg_off = ix->ctg_off.as<uint32_t>(); v.ctg_id = ix->ctg_id.as<int32_t>(); v.ctg_rank = ix->ctg_rank.as<int32_t>();
     CK(cudaDeviceSynchronize());
+}
+
+// Locate table with the suffix-array value of every `step`-th row (1, 2, 4, 8 or 16; GW_SSA_L drops the table), built on the device
+// from the index itself. step 0: the densest table that takes at most a fifth of the free device memory.
+void densify_index(gw_index* ix, int step) {
+    CK(cudaSetDevice(ix->device));
+    if (step == 0) {
+        size_t free_b = 0, total_b = 0;
+        CK(cudaMemGetInfo(&free_b, &total_b));
+        step = 1;
+        while (step < GW_SSA_L && 2.0 * 4.0 * (double)((ix->N + step - 1) / step) > 0.2 * (double)free_b) step *= 2;
+    }
+    GwIndexView& v = ix->view;
+    for (int s = 0; s < 2; ++s) { v.loc[s] = v.ssa[s]; ix->loc[s].release(); }
+    v.loc_step = GW_SSA_L;
+    if (step >= GW_SSA_L || ix->N == 0) return;
+    for (int s = 0; s < 2; ++s) {
+        const size_t entries = (size_t)((ix->N + step - 1) / step);
+        ix->loc[s].ensure(entries * 4);
+        CK(cudaMemset(ix->loc[s].p, 0xFF, entries * 4));
+        gwk_densify(0, v, s, (uint32_t)step, ix->loc[s].as<uint32_t>(), v.n_ssa);
+    }
+    CK(cudaDeviceSynchronize());
+    CK(cudaGetLastError());
+    for (int s = 0; s < 2; ++s) v.loc[s] = ix->loc[s].as<uint32_t>();
+    v.loc_step = (uint32_t)step;
 }
 
 std::vector<uint8_t> codes_of(const char* bases, uint64_t n) {
@@ -157,11 +186,20 @@ int gw_index_open(const char* fasta_path, int device, gw_index_t** out) {
         GwHostIndex h;
         gw_load_index_files(fasta_path, h);
         gw_index* ix = new gw_index();
-        try { make_device_index(ix, h, device); } catch (...) { delete ix; throw; }
+        try { make_device_index(ix, h, device); densify_index(ix, 0); } catch (...) { delete ix; throw; }
         *out = ix;
         return GW_OK;
     });
 }
+
+int gw_index_locate_table(gw_index_t* ix, int step) {
+    return guarded([&]() -> int {
+        if (!ix || step < 0 || step > GW_SSA_L || (step & (step - 1)) != 0) return fail(GW_E_ARG, "step must be 0 (automatic), 1, 2, 4, 8, 16 or 32");
+        densify_index(ix, step);
+        return GW_OK;
+    });
+}
+int gw_index_locate_step(const gw_index_t* ix) { return ix ? (int)ix->view.loc_step : -1; }
 
 int gw_index_from_sequence(const char* name, const char* bases, int device, gw_index_t** out) {
     return guarded([&]() -> int {
@@ -177,7 +215,7 @@ int gw_index_from_sequence(const char* name, const char* bases, int device, gw_i
         h.contigs.push_back(c);
         gw_build_host_index(device, h);
         gw_index* ix = new gw_index();
-        try { make_device_index(ix, h, device); } catch (...) { delete ix; throw; }
+        try { make_device_index(ix, h, device); densify_index(ix, 0); } catch (...) { delete ix; throw; }
         *out = ix;
         return GW_OK;
     });

@@ -3,7 +3,7 @@
 // points where the reference calls into the sampled suffix array and the verifier (verify :496-560). At those points the
 // read parks with up to two fragment requests; the verification batch of the flow kernel fills them and the read resumes.
 //
-// Two kinds of code live here. The HOT slices (gw_lane_poll, gw_lane_try) run on the lane's register copy of the read
+// Two kinds of code live here. The HOT slices (gw_lane_poll, gw_lane_try) run on the lane's record of the read
 // (GwLane, gw_search.cuh) and are written to stay small and branch-poor: they are the loop every search step goes through.
 // The COLD continuations (taking a read up, reporting a chain, split / soft-clip children) are out-of-line functions that work on
 // the read's work area in HBM; the caller writes the lane back before and re-reads it after them.
@@ -263,7 +263,7 @@ GW_HD int gw_lane_poll(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln
     return GW_STEP_CONTINUE;
 }
 
-// ONE candidate extension of the state in the lane's registers: candidate choice (:415-455), Cursor.nextSi +
+// ONE candidate extension of the state in the lane's record: candidate choice (:415-455), Cursor.nextSi +
 // FMIndexOnGenome.bidirectionalSearch (two rank queries on one index, FMIndexOnGenome.java:148-194), ReadAlignmentNFA.nextState +
 // SearchState.nextState (ReadAlignmentNFA.java:146-215), queue insertion. MAXH: compile-time bound of the NFA height (k + 1): for
 // MAXH <= 8 the rows stay in registers (every loop over rows is unrolled with constant indices).
@@ -308,10 +308,7 @@ GW_HD int gw_lane_try(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln)
     // ---- Cursor.nextSi + bidirectionalSearch
     bool hasF = kindF && ((C.f_valid >> ch) & 1), hasB = kindB && ((C.b_valid >> ch) & 1);
     if (dir == GW_DIR_BF && C.cursor >= C.end - 1) hasF = false;
-    uint32_t f_lb = 0, f_ub = 0, b_lb = 0, b_ub = 0;   // intervals of `ch`, selected without indexing by a run-time value
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-        if (i == ch) { f_lb = C.sif[i][0]; f_ub = C.sif[i][1]; b_lb = C.sib[i][0]; b_ub = C.sib[i][1]; }
+    const uint32_t f_lb = C.sif[ch][0], f_ub = C.sif[ch][1], b_lb = C.sib[ch][0], b_ub = C.sib[ch][1];   // intervals of `ch`
     GwState n;   // the child
 #pragma unroll
     for (int i = 0; i < 4; ++i) { n.sif[i][0] = n.sif[i][1] = 0; n.sib[i][0] = n.sib[i][1] = 0; }
@@ -352,8 +349,13 @@ GW_HD int gw_lane_try(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln)
     const int fragmentLength = C.end - C.start;
     const int progressIndex = fwdC ? C.cursor - C.pivot : C.end - C.cursor;
     const int sf_offset = progressIndex - k;
-    const u64* prev = ln.rows;
-    u64 next[MAXH];
+    u64 prev[MAXH], next[MAXH];
+    if constexpr (MAXH <= 8) {
+#pragma unroll
+        for (int i = 0; i < MAXH; ++i) prev[i] = ln.row(i);
+    } else {
+        for (int i = 0; i < height; ++i) prev[i] = ln.row(i);
+    }
     int minKwithMatch = k + 1, minKwithProgress = k + 1;
     next[0] = (prev[0] & qeq) << 1;
     if (next[0] != 0) { minKwithMatch = 0; minKwithProgress = 0; }
@@ -437,7 +439,7 @@ GW_HD int gw_lane_try(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln)
     }
     {   // written through to the arena
         GwState* np = gw_st(s, off);
-        *np = n;
+        gw_state_put(np, n);
         u64* nr = gw_rows(np);
         if constexpr (MAXH <= 8) {
 #pragma unroll
@@ -446,13 +448,17 @@ GW_HD int gw_lane_try(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln)
             for (int h = 0; h < newHeight; ++h) nr[h] = nrows[h];
         }
     }
-    // the usual case — a chain of one state — takes its queue key from the register copy of the state just built
+    // the usual case — a chain of one state — takes its queue key from the state just built, still in registers
     const bool ok = exclusive ? gw_lq_add(s, ln, off, gw_state_key_single(cfg, &n)) : gw_lane_chain_insert(env, s, ln, off);
     if (!ok) { gw_fail(c, GW_ST_OVERFLOW); return GW_STEP_DONE; }
     if (own) {   // extended: the parent is dropped (:426-429), the step is over; the child is most likely the next state polled
         ln.C = n;
+        if constexpr (MAXH <= 8) {
 #pragma unroll
-        for (int j = 0; j < MAXH; ++j) ln.rows[j] = nrows[j];
+            for (int j = 0; j < MAXH; ++j) ln.set_row(j, nrows[j]);
+        } else {
+            for (int j = 0; j < newHeight; ++j) ln.set_row(j, nrows[j]);
+        }
         ln.cached = off;
         ln.mid = 0;
     }

@@ -59,7 +59,13 @@ struct GwU64x2 { u64 x, y; };
 // device view of an opened index
 struct GwIndexView {
     const GwOccBlock* occ[2];   // [0] BWT of the text ("forward index"), [1] BWT of the reversed text ("reverse index")
-    const uint32_t* ssa[2];     // SA samples every GW_SSA_L rows
+    const uint32_t* ssa[2];     // SA samples every GW_SSA_L rows (the reference's .ssa files)
+    // locate table: the suffix-array value of every loc_step-th row (loc_step a power of two <= GW_SSA_L). It is the .ssa samples
+    // themselves (loc_step == GW_SSA_L) until gw_index_open densifies it on the device: HBM has room for the whole suffix array of a
+    // human-scale genome, and a locate then costs one 4-byte gather instead of a walk of ~31 dependent occurrence-block gathers.
+    // 0xFFFFFFFF marks a row the table does not know (only possible for rows no LF walk from a sampled row passes through).
+    const uint32_t* loc[2];
+    uint32_t loc_step;
     uint32_t C[2][5];           // CharacterCount.C per index
     uint32_t N;                 // text length (all contigs concatenated)
     uint32_t n_ssa;

@@ -91,15 +91,24 @@ GW_HD uint32_t gw_suffix_link(const GwIndexView& ix, int fm, uint32_t index) {
     return ix.C[fm][ch] + gw_rank1(b, r, ch);
 }
 
-// SparseSuffixArray.get: text position of SA row `index`; *steps receives the number of LF steps (occ lookups)
+// SparseSuffixArray.get: text position of SA row `index`; *steps receives the number of LF steps (occ lookups) it took.
+// With the locate table at its densest (loc_step == 1) no step is taken at all.
 GW_HD uint32_t gw_sa_get(const GwIndexView& ix, int fm, uint32_t index, uint32_t* steps) {
     uint32_t cursor = index, j = 0;
-    while ((cursor % GW_SSA_L) != 0) {
+    const uint32_t mask = ix.loc_step - 1u;
+    while ((cursor & mask) != 0) {
         cursor = gw_suffix_link(ix, fm, cursor);
         ++j;
     }
+    uint32_t s = gw_ld32(ix.loc[fm] + cursor / ix.loc_step);
+    if (s == 0xFFFFFFFFu) {   // unknown to the table: the reference's own walk to a sampled row
+        while ((cursor % GW_SSA_L) != 0) {
+            cursor = gw_suffix_link(ix, fm, cursor);
+            ++j;
+        }
+        s = gw_ld32(ix.ssa[fm] + cursor / GW_SSA_L);
+    }
     *steps = j;
-    const uint32_t s = gw_ld32(ix.ssa[fm] + cursor / GW_SSA_L);
     if (j == 0) return s;
     return (uint32_t)(((u64)s + j + ix.N) % ix.N);
 }

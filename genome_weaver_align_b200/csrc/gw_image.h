@@ -77,6 +77,7 @@ inline void gw_layout_index(const GwHostIndex& h, GwIndexImage& img) {
         }
     }
     v.n_ssa = (uint32_t)h.ssa[0].size();
+    v.loc_step = GW_SSA_L;   // the locate table is the row samples until the device densifies it (gw_api.cu)
     const size_t nw = (size_t)(h.N / 64) + 1;
     img.ref_lo.assign(nw, 0); img.ref_hi.assign(nw, 0); img.ref_nf.assign(nw, 0);
     {

@@ -97,9 +97,6 @@ __global__ void __launch_bounds__(256) gw_scan_coop_kernel(GwIndexView ix, u64* 
 #ifndef GW_FLOW_THREADS
 #define GW_FLOW_THREADS 256
 #endif
-#ifndef GW_FLOW_MINB
-#define GW_FLOW_MINB 2
-#endif
 #define GW_RING 128     // entries per FIFO; a warp owns at most GW_RING reads (refill stops above GW_RING - 32), at most 95 fragments wait
 #define GW_WARPS (GW_FLOW_THREADS / 32)
 
@@ -110,23 +107,27 @@ struct GwFlowParams {
     uint32_t flush;      // once the work list is drained, a partial verification batch runs when this many lanes idle
 };
 
+// dynamic shared memory of a CTA: the two FIFOs of every warp, then one GwLane record per thread (odd word stride)
+extern __shared__ uint32_t gw_flow_smem[];
 template <int MAXH>
-__global__ void __launch_bounds__(GW_FLOW_THREADS, GW_FLOW_MINB) gw_flow_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
+static size_t gw_flow_smem_bytes() { return ((size_t)2 * GW_WARPS * GW_RING + (size_t)GW_FLOW_THREADS * GW_LANE_WORDS(MAXH)) * 4; }
+
+// MINB: CTAs per SM the kernel is compiled for (register cap 65536 / (MINB * 256))
+template <int MAXH, int MINB>
+__global__ void __launch_bounds__(GW_FLOW_THREADS, MINB) gw_flow_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
                                                                   uint32_t* work_counter, GwU64x2* hist, GwFlowParams pp) {
-    __shared__ uint32_t ready_s[GW_WARPS][GW_RING];
-    __shared__ uint32_t frags_s[GW_WARPS][GW_RING];
     const uint32_t FULL = 0xFFFFFFFFu, MASK = GW_RING - 1u;
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
-    uint32_t* ready = ready_s[wid];
-    uint32_t* frags = frags_s[wid];
+    uint32_t* ready = gw_flow_smem + wid * GW_RING;
+    uint32_t* frags = gw_flow_smem + (GW_WARPS + wid) * GW_RING;
+    GwLane<MAXH>& ln = *reinterpret_cast<GwLane<MAXH>*>(gw_flow_smem + 2 * GW_WARPS * GW_RING + threadIdx.x * GW_LANE_WORDS(MAXH));
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_pick = 0, age_cold = 0, owned = 0;
     bool drained = false;
     bool have = false;
     GwSlab s;
-    GwLane<MAXH> ln;
     ln.mid = 0; ln.top = 0; ln.k = 0;
     uint32_t slot = 0;
     for (;;) {
@@ -143,13 +144,9 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, GW_FLOW_MINB) gw_flow_kernel(
             if (lane < nb) {   // locate
                 c = reinterpret_cast<GwReadCtx*>(slabs[id >> 1]);
                 GwPendFrag* pf = &c->pend[id & 1u];
-                uint32_t cursor = pf->sa_index;
-                const int fm = pf->fm;
-                int j = 0;
-                while ((cursor % GW_SSA_L) != 0) { cursor = gw_suffix_link(env.ix, fm, cursor); ++j; }
-                const uint32_t smp = gw_ld32(env.ix.ssa[fm] + cursor / GW_SSA_L);
-                pf->textpos = j == 0 ? smp : (uint32_t)(((u64)smp + (u64)j + env.ix.N) % env.ix.N);
-                atomicAdd(&c->occ_locate, (uint32_t)j);   // the two fragments of a read are walked by different lanes
+                uint32_t j = 0;
+                pf->textpos = gw_sa_get(env.ix, pf->fm, pf->sa_index, &j);
+                if (j) atomicAdd(&c->occ_locate, j);   // the two fragments of a read are walked by different lanes
             }
             __syncwarp();
             {   // DP + traceback; the lanes take the DP instantiation of the largest block count among them
@@ -268,6 +265,26 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, GW_FLOW_MINB) gw_flow_kernel(
         }
         owned -= (uint32_t)__popc(__ballot_sync(FULL, have && r == GW_STEP_DONE));
         if (have && r != GW_STEP_CONTINUE) have = false;
+    }
+}
+
+// Densifies the locate table of one index. The LF walk that starts at a sampled row (a multiple of GW_SSA_L) passes through every row
+// whose own walk ends at the NEXT sampled row it reaches — the rows SparseSuffixArray.get resolves with that sample
+// (SparseSuffixArray.java:141-161). One thread per sampled row walks twice: once to find that next sample and the distance to it,
+// once to store, for every row of the walk that is a multiple of `step`, the value the reference computes there:
+// (sample + remaining steps + N) % N. The walks of all threads together visit every row once (LF is a permutation).
+__global__ void __launch_bounds__(256) gw_densify_kernel(GwIndexView ix, int fm, uint32_t step, uint32_t* table, uint32_t n_samples) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_samples) return;
+    const uint32_t start = t * GW_SSA_L;
+    table[start / step] = gw_ld32(ix.ssa[fm] + t);
+    uint32_t cursor = gw_suffix_link(ix, fm, start), len = 1;
+    while ((cursor % GW_SSA_L) != 0) { cursor = gw_suffix_link(ix, fm, cursor); ++len; }
+    const uint32_t smp = gw_ld32(ix.ssa[fm] + cursor / GW_SSA_L);
+    cursor = gw_suffix_link(ix, fm, start);
+    for (uint32_t i = 1; i < len; ++i) {   // row `cursor` reaches the sample after len - i steps
+        if ((cursor & (step - 1u)) == 0) table[cursor / step] = (uint32_t)(((u64)smp + (u64)(len - i) + ix.N) % ix.N);
+        cursor = gw_suffix_link(ix, fm, cursor);
     }
 }
 
@@ -448,23 +465,34 @@ void gwk_scan(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const u
     if (coop) gw_scan_coop_kernel<<<gw_grid(n_tasks * 4, 256), 256, 0, st>>>(ix, slabs, slots, (uint32_t)n_tasks);
     else gw_scan_kernel<<<gw_grid(n_tasks, 128), 128, 0, st>>>(ix, slabs, slots, (uint32_t)n_tasks);
 }
-void gwk_flow_setup(void) {
-    // two CTAs need 18 KB for their FIFOs: the smallest fitting shared-memory configuration leaves 224 KB of each SM to the L1, where
-    // the per-read work areas live. Function attributes are per device: called once per aligner (after cudaSetDevice).
-    const int pct = 14;
-    cudaFuncSetAttribute(gw_flow_kernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-    cudaFuncSetAttribute(gw_flow_kernel<8>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-    cudaFuncSetAttribute(gw_flow_kernel<GW_MAX_ROWS>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+template <int MAXH, int MINB>
+static void gw_flow_attr() {
+    // the lane records take most of the shared memory the CTAs of an SM ask for; the rest of the SM's 256 KB is L1 for the work areas
+    const size_t bytes = gw_flow_smem_bytes<MAXH>();
+    cudaFuncSetAttribute(gw_flow_kernel<MAXH, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    int pct = (int)((bytes + 1024) * MINB * 100 / (228 * 1024)) + 1;
+    cudaFuncSetAttribute(gw_flow_kernel<MAXH, MINB>, cudaFuncAttributePreferredSharedMemoryCarveout, pct > 100 ? 100 : pct);
 }
+void gwk_flow_setup(void) {   // function attributes are per device: called once per aligner (after cudaSetDevice)
+    gw_flow_attr<4, 2>(); gw_flow_attr<4, 3>(); gw_flow_attr<8, 2>(); gw_flow_attr<8, 3>(); gw_flow_attr<GW_MAX_ROWS, 2>();
+}
+int gwk_flow_ctas(int maxh, int want) { return (maxh <= 8 && want >= 3) ? 3 : 2; }
 void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-              uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh) {
+              uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh, int ctas) {
     if (!n_active) return;
     GwFlowParams pp;
     pp.cap = fetch < 1 ? 1 : (fetch > 32 ? 32 : fetch);
     pp.batch = batch < 1 ? 1 : batch; pp.age = age < 1 ? 1 : age; pp.flush = flush < 1 ? 1 : flush;
-    if (maxh <= 4) gw_flow_kernel<4><<<blocks, GW_FLOW_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
-    else if (maxh <= 8) gw_flow_kernel<8><<<blocks, GW_FLOW_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
-    else gw_flow_kernel<GW_MAX_ROWS><<<blocks, GW_FLOW_THREADS, 0, st>>>(env, slabs, active, n_active, work_counter, (GwU64x2*)hist, pp);
+    GwU64x2* h = (GwU64x2*)hist;
+    const bool three = gwk_flow_ctas(maxh, ctas) == 3;
+#define GW_FLOW_LAUNCH(H, B) gw_flow_kernel<H, B><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<H>(), st>>>(env, slabs, active, n_active, work_counter, h, pp)
+    if (maxh <= 4) { if (three) GW_FLOW_LAUNCH(4, 3); else GW_FLOW_LAUNCH(4, 2); }
+    else if (maxh <= 8) { if (three) GW_FLOW_LAUNCH(8, 3); else GW_FLOW_LAUNCH(8, 2); }
+    else GW_FLOW_LAUNCH(GW_MAX_ROWS, 2);
+#undef GW_FLOW_LAUNCH
+}
+void gwk_densify(cudaStream_t st, const GwIndexView& ix, int fm, uint32_t step, uint32_t* table, uint32_t n_samples) {
+    if (n_samples) gw_densify_kernel<<<gw_grid(n_samples, 256), 256, 0, st>>>(ix, fm, step, table, n_samples);
 }
 void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count) {
     if (n) gw_collect_overflow_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, list, count);

@@ -117,7 +117,7 @@ GW_HD int32_t gw_alloc_state(const GwSlab& s, int height) {
     return gw_alloc(s, gw_state_words(c->k));
 }
 // whole-state copy from / to the arena (six 128-bit accesses; states are 16-byte aligned)
-GW_HD GwState gw_load_state(const GwSlab& s, int32_t off) { return *gw_st(s, off); }
+GW_HD GwState gw_load_state(const GwSlab& s, int32_t off) { GwState st; gw_state_get(st, gw_st(s, off)); return st; }
 
 GW_HD void gw_set_init_siset(const GwIndexView& ix, GwState* st, int dir) {
     st->f_valid = st->b_valid = 0;
@@ -146,7 +146,7 @@ GW_HD int32_t gw_initial_state(const GwSearchEnv& env, const GwSlab& s, int stra
     st.state = gw_pack_state(4, minK, priority, false);
     st.next_split = -1;
     st.cur_lb = st.cur_ub = 0;
-    *gw_st(s, off) = st;
+    gw_state_put(gw_st(s, off), st);
     u64* rows = gw_rows(gw_st(s, off));
     for (int i = 0; i <= k; ++i) rows[i] = jshl(1ULL, k + i);
     return off;
@@ -159,27 +159,36 @@ GW_HD bool gw_si_is_empty(const GwState* c, int ch) {
 }
 
 // ---- search lane -------------------------------------------------------------------------------------------
-// A lane (one thread) drives one read at a time. What every step of the best-first loop touches lives in the lane's registers
-// while the lane owns the read: the counters and cursors of the context, the root of the priority queue, and the state that is
-// being extended (`C`, with its NFA rows). The work area in HBM stays the canonical copy for everything else; the lane's copy is
-// written back (gw_lane_flush) before any of the out-of-line continuations runs on the work area and re-read after it
-// (gw_lane_reload). States are written through to the arena when they are built, so `cached` only ever saves the load:
-// after an extension with the read's own base the child is the next state polled nearly every time, and it is already here.
+// A lane (one thread) drives one read at a time. What every step of the best-first loop touches is kept in a small per-lane
+// record while the lane owns the read: the counters and cursors of the context, the root of the priority queue, and the state
+// that is being extended (`C`, with its NFA rows). In the flow kernel these records live in SHARED memory, one per thread at an odd
+// word stride (all members are 32-bit, so the lanes of a warp never collide on a bank): the lane's hot data costs neither registers
+// (which would cap the SM at a quarter of its warps) nor L1 lines, and the run-time indexed accesses of a step (the interval of the
+// candidate base, the NFA row to cut at) are plain indexed loads. The work area in HBM stays the canonical copy for everything else;
+// the lane's record is written back (gw_lane_flush) before any of the out-of-line continuations runs on the work area and re-read
+// after it (gw_lane_reload). States are written through to the arena when they are built, so `cached` only ever saves the load: after
+// an extension with the read's own base the child is the next state polled nearly every time, and it is already here.
 template <int MAXH>
 struct GwLane {
     int32_t m, k, min_mm, best_score;
     int32_t n_fm, n_cut, n_filt;
     int32_t qn, top, free1;
     int32_t sf_mm, sf_off;      // staircase table of minMismatches == sf_mm: word offset, -1: the reference throws
-    u64 root_key;               // queue entry 0 (valid while qn > 0)
+    uint32_t root_key_lo, root_key_hi;   // queue entry 0 (valid while qn > 0)
     int32_t root_off;
     int32_t base;               // polled queue entry (head of the split chain)
     int32_t c_off;              // fragment of the chain that is being extended
     int32_t mid;                // GW_MID_*: what remains of the current step
     int32_t cached;             // arena offset whose state C / rows hold, -1: none
     GwState C;
-    u64 rows[MAXH];
+    uint32_t rows[2 * MAXH];    // NFA rows of C as (low, high) words
+    GW_HD u64 root_key() const { return (u64)root_key_lo | ((u64)root_key_hi << 32); }
+    GW_HD void set_root(u64 key, int32_t off) { root_key_lo = (uint32_t)key; root_key_hi = (uint32_t)(key >> 32); root_off = off; }
+    GW_HD u64 row(int i) const { return (u64)rows[2 * i] | ((u64)rows[2 * i + 1] << 32); }
+    GW_HD void set_row(int i, u64 v) { rows[2 * i] = (uint32_t)v; rows[2 * i + 1] = (uint32_t)(v >> 32); }
 };
+#define GW_LANE_WORDS(MAXH) ((uint32_t)(sizeof(GwLane<MAXH>) / 4))
+static_assert(GW_LANE_WORDS(4) % 2 == 1 && GW_LANE_WORDS(8) % 2 == 1 && GW_LANE_WORDS(GW_MAX_ROWS) % 2 == 1, "odd word stride: conflict-free lanes");
 
 #define GW_MID_TRY 1
 #define GW_MID_SPLIT 2
@@ -192,7 +201,7 @@ GW_HD void gw_lane_reload(const GwSlab& s, GwLane<MAXH>& ln) {
     ln.n_fm = c->n_fm; ln.n_cut = c->n_cut; ln.n_filt = c->n_filt;
     ln.qn = c->qn; ln.top = c->top; ln.free1 = c->free1;
     const GwQEntry r = s.queue()[0];
-    ln.root_key = r.key; ln.root_off = r.off;
+    ln.set_root(r.key, r.off);
 }
 template <int MAXH>
 GW_HD void gw_lane_load(const GwSlab& s, GwLane<MAXH>& ln) {
@@ -208,25 +217,26 @@ GW_HD void gw_lane_flush(const GwSlab& s, const GwLane<MAXH>& ln) {
     GwReadCtx* c = s.ctx();
     c->n_fm = ln.n_fm; c->n_cut = ln.n_cut; c->n_filt = ln.n_filt;
     c->qn = ln.qn; c->top = ln.top; c->free1 = ln.free1;
-    if (ln.qn > 0) { GwQEntry r; r.key = ln.root_key; r.off = ln.root_off; r.pad_ = 0; s.queue()[0] = r; }
+    if (ln.qn > 0) { GwQEntry r; r.key = ln.root_key(); r.off = ln.root_off; r.pad_ = 0; s.queue()[0] = r; }
 }
 
-// the state at `off` into the lane's registers
+// the state at `off` into the lane's record
 template <int MAXH>
 GW_HD void gw_lane_fetch(const GwSlab& s, GwLane<MAXH>& ln, int32_t off) {
     GwState* p = gw_st(s, off);
-    ln.C = *p;
+    gw_state_get(ln.C, p);
     const u64* rows = gw_rows(p);
+    const int height = ln.C.height;
     if constexpr (MAXH <= 8) {
 #pragma unroll
-        for (int i = 0; i < MAXH; ++i) ln.rows[i] = i < ln.C.height ? rows[i] : 0ULL;
+        for (int i = 0; i < MAXH; ++i) ln.set_row(i, i < height ? rows[i] : 0ULL);
     } else {
-        for (int i = 0; i < ln.C.height; ++i) ln.rows[i] = rows[i];
+        for (int i = 0; i < height; ++i) ln.set_row(i, rows[i]);
     }
     ln.cached = off;
 }
 
-// java.util.PriorityQueue.offer / poll as above, with entry 0 in the lane's registers
+// java.util.PriorityQueue.offer / poll as above, with entry 0 in the lane's record
 template <int MAXH>
 GW_HD bool gw_lq_add(const GwSlab& s, GwLane<MAXH>& ln, int32_t e, const u64 ke) {
     GwQEntry* q = s.queue();
@@ -240,12 +250,12 @@ GW_HD bool gw_lq_add(const GwSlab& s, GwLane<MAXH>& ln, int32_t e, const u64 ke)
         q[k] = p;
         k = parent;
     }
-    if (k > 0 && k <= 2 && ke < ln.root_key) {   // the parent is the root
-        GwQEntry p; p.key = ln.root_key; p.off = ln.root_off; p.pad_ = 0;
+    if (k > 0 && k <= 2 && ke < ln.root_key()) {   // the parent is the root
+        GwQEntry p; p.key = ln.root_key(); p.off = ln.root_off; p.pad_ = 0;
         q[k] = p;
         k = 0;
     }
-    if (k == 0) { ln.root_key = ke; ln.root_off = e; }
+    if (k == 0) ln.set_root(ke, e);
     else { GwQEntry n; n.key = ke; n.off = e; n.pad_ = 0; q[k] = n; }
     return true;
 }
@@ -264,10 +274,10 @@ GW_HD int32_t gw_lq_poll(const GwSlab& s, GwLane<MAXH>& ln) {
             GwQEntry cc = q[child];
             if (right < n) { const GwQEntry cr = q[right]; if (cc.key > cr.key) { cc = cr; child = right; } }
             if (x.key <= cc.key) break;
-            if (k == 0) { ln.root_key = cc.key; ln.root_off = cc.off; } else q[k] = cc;
+            if (k == 0) ln.set_root(cc.key, cc.off); else q[k] = cc;
             k = child;
         }
-        if (k == 0) { ln.root_key = x.key; ln.root_off = x.off; } else q[k] = x;
+        if (k == 0) ln.set_root(x.key, x.off); else q[k] = x;
     }
     return result;
 }
@@ -331,10 +341,10 @@ GW_COLD int32_t gw_split_state(const GwSearchEnv& env, const GwSlab& s, const Gw
         r.height = 0; r.k_offset = 0; r.has_nfa = 0;
         r.state = gw_pack_state(4, minK, gw_priority(&c), false) | (1 << 25);
         r.next_split = -1;
-        *gw_st(s, roff) = r;
+        gw_state_put(gw_st(s, roff), r);
     }
     l.next_split = roff;
-    *gw_st(s, loff) = l;
+    gw_state_put(gw_st(s, loff), l);
     u64* lr = gw_rows(gw_st(s, loff));
     for (int i = 0; i < newHeight; ++i) lr[i] = jshl(1ULL, newHeight + i - 1);  // ReadAlignmentNFA.nextStateAfterSplit
     return loff;

@@ -92,7 +92,10 @@ struct GwSlab {
 #define GW_DIR_B 1
 #define GW_DIR_BF 2
 
-struct alignas(16) GwState {
+// 4-byte alignment only: the search lanes keep a copy of the state they extend in shared memory at an odd word stride (no bank
+// conflicts between the lanes of a warp); in the arena states sit on 16-byte boundaries and are moved with 128-bit accesses
+// (gw_state_put / gw_state_get).
+struct GwState {
     int16_t start, end, cursor, pivot;   // Cursor
     uint8_t cflag;                       // strand | dir << 1
     uint8_t si_kind;
@@ -109,6 +112,10 @@ struct alignas(16) GwState {
 };
 #define GW_STATE_WORDS ((uint32_t)((sizeof(GwState) + 7) / 8))
 
+static_assert(sizeof(GwState) == 96, "GwState is 24 words");
+// whole-state copies between the arena (16-byte aligned) and a lane's copy (4-byte aligned)
+GW_HD void gw_state_put(GwState* arena, const GwState& src) { memcpy(__builtin_assume_aligned(arena, 16), &src, sizeof(GwState)); }
+GW_HD void gw_state_get(GwState& dst, const GwState* arena) { memcpy(&dst, __builtin_assume_aligned(arena, 16), sizeof(GwState)); }
 GW_HD u64* gw_rows(GwState* s) { return reinterpret_cast<u64*>(s) + GW_STATE_WORDS; }
 GW_HD int gw_strand(const GwState* s) { return s->cflag & 1; }
 GW_HD int gw_dir(const GwState* s) { int d = (s->cflag >> 1) & 3; return d == 3 ? GW_DIR_F : d; }

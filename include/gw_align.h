@@ -90,6 +90,12 @@ int gw_index_build(const char* fasta_path, int device);
 /* FMIndexOnGenome.load + ACGTSequence.loadFrom(.f.3bit) (align/FMIndexOnGenome.java:60-86, align/Align.java:159-170):
  * reads the reference's index files and lays them out in HBM of `device`. */
 int gw_index_open(const char* fasta_path, int device, gw_index_t** out);
+/* Locate table in HBM: the suffix-array value of every step-th row (step 1, 2, 4, 8, 16; 32 = the .ssa samples alone, as
+ * SparseSuffixArray.get uses them, align/SparseSuffixArray.java:141-161; 0 = the densest table that fits a fifth of the free device
+ * memory, which gw_index_open applies). Built on the device from the opened index; results of every call are unchanged by it, a
+ * locate just takes fewer (with step 1: no) LF steps. */
+int gw_index_locate_table(gw_index_t*, int step);
+int gw_index_locate_step(const gw_index_t*);
 /* FMIndexOnGenome.buildFromSequence (align/FMIndexOnGenome.java:104-119): single contig from an ACGTN string, no files. */
 int gw_index_from_sequence(const char* name, const char* bases, int device, gw_index_t** out);
 void gw_index_close(gw_index_t*);

@@ -46,7 +46,7 @@ void* gwsim_open(const char* fasta_path) {
         gw_load_index_files(fasta_path, s->host);
         gw_layout_index(s->host, s->img);
         s->view = s->img.view;
-        for (int i = 0; i < 2; ++i) { s->view.occ[i] = s->img.occ[i].data(); s->view.ssa[i] = s->host.ssa[i].data(); }
+        for (int i = 0; i < 2; ++i) { s->view.occ[i] = s->img.occ[i].data(); s->view.ssa[i] = s->host.ssa[i].data(); s->view.loc[i] = s->view.ssa[i]; }
         s->view.ref_lo = s->img.ref_lo.data(); s->view.ref_hi = s->img.ref_hi.data(); s->view.ref_nf = s->img.ref_nf.data();
         s->view.ctg_off = s->img.ctg_off.data(); s->view.ctg_id = s->img.ctg_id.data(); s->view.ctg_rank = s->img.ctg_rank.data();
         return s;

@@ -160,13 +160,34 @@ def test_rank_and_locate(small):
             assert int(l) == oidx.locate(which, int(r))
 
 
+def test_locate_table_steps(small):
+    # the locate table built on the device (suffix-array value of every step-th row) must give what SparseSuffixArray.get gives,
+    # whatever its density; alignment results must not depend on it either
+    idx, oidx = small["idx"], small["oidx"]
+    N = idx.textSize()
+    assert idx.locateStep() == 1   # what load() chose: the whole suffix array fits easily
+    rnd = np.random.default_rng(2)
+    rows = np.concatenate([rnd.integers(0, N, size=3000), [0, 1, 31, 32, 33, N - 1]]).astype(np.uint32)
+    want = [oidx.locate(0, int(r)) for r in rows[::3]], [oidx.locate(1, int(r)) for r in rows[::3]]
+    reads = synth.simulate_reads(small["g"], 800, 100, 3, 41)
+    try:
+        for step in (1, 2, 16, 32, 4):
+            idx.locateTable(step)
+            assert idx.locateStep() == step
+            for which in (0, 1):
+                assert [int(x) for x in idx.locate(which, rows)[::3]] == want[which], (step, which)
+            batch, _ = compare(idx, oidx, reads, gw.AlignmentConfig(k=3), dict(k=3))
+            assert (batch.counters["occ_lookups_locate"] == 0) == (step == 1)
+    finally:
+        idx.locateTable(0)
+
+
 @pytest.mark.parametrize("coop", [0, 1])
-def test_quick_scan_both_forms(small, coop, monkeypatch):
-    monkeypatch.setenv("GW_SCAN_COOP", str(coop))
+def test_quick_scan_both_forms(small, coop):
     reads = synth.simulate_reads(small["g"], 300, 100, 3, 40) + ["ACGT", "A", "ACGTNACGT" * 3]
     import ctypes as C
     for strand in (0, 1):
-        got = small["idx"].quickScan(reads, strand)
+        got = small["idx"].quickScan(reads, strand, coop)
         for i in range(0, len(reads), 7):
             q = reads[i].replace("N", "A")
             if strand == 1:
