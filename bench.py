@@ -214,6 +214,8 @@ def run_ours(args):
     barrier()
     fa = os.path.join(cache_dir(args), "genome.fa")
     idx = gw.FMIndexOnGenome.load(fa, local)
+    if args.locate_step is not None:
+        idx.locateTable(args.locate_step)
     reads = make_reads(args, genome, rank)
     n, m = reads.shape
     offsets = (np.arange(n + 1, dtype=np.uint64) * np.uint64(m))
@@ -327,7 +329,7 @@ def run_ours(args):
                            l2="working set (index %.2f GB + per-read work areas of several GB rewritten every step) exceeds the 126 MB L2; no explicit flush" % (
                                (genome.size / 128 * 64 * 2 + genome.size / 8 + genome.size * 3 / 8) / 1e9),
                            parallelism="reads sharded over %d GPU(s), index replicated, no collective" % world, index_built_by=how,
-                           index_build_s=round(t_build, 2)),
+                           index_build_s=round(t_build, 2), locate_table_step=idx.locateStep()),
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
                          "peak_source": peak_src, "random_gather_gbs": gather, "frac_of_random_gather": (ach / gather if gather else None),
                          "note": "algorithmic bytes = occurrence-table lookups x 64 B (+4 B per SA sample) over the CUDA-event time of the kernel family; "
@@ -377,6 +379,7 @@ def main():
     ap.add_argument("--ref-sample", type=int, default=200_000)
     ap.add_argument("--cache", default="/tmp")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--locate-step", type=int, default=None, help="density of the locate table (1..32; default: what gw_index_open chooses)")
     ap.add_argument("--opt", action="append", default=[], help="aligner option name=value (e.g. scan_coop=0)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -63,7 +63,7 @@ SYMBOLS = {
     "gw_gather_benchmark": (C.c_int, [_P, C.c_int, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "gw_rank_acgtn": (C.c_int, [_P, C.c_int, _P, C.c_uint32, _P]),
     "gw_locate": (C.c_int, [_P, C.c_int, _P, C.c_uint32, _P]),
-    "gw_quick_scan": (C.c_int, [_P, _P, _P, C.c_uint32, C.c_int, _P]),
+    "gw_quick_scan": (C.c_int, [_P, _P, _P, C.c_uint32, C.c_int, C.c_int, _P]),
     "gw_verify_pairs": (C.c_int, [C.c_int, _P, _P, _P, _P, C.c_uint32, C.c_int, _P, _P, C.c_uint32]),
     "gw_staircase_table": (C.c_int, [C.c_int, C.c_int, _P, C.c_int]),
     "gw_cyclic_suffix_array": (C.c_int, [_P, C.c_uint64, C.c_int, _P]),

@@ -103,10 +103,10 @@ class FMIndexOnGenome:
         L.check(L.lib().gw_locate(self._h, which, L.ptr(rows), len(rows), L.ptr(out)))
         return out
 
-    def quickScan(self, seqs, strand):
+    def quickScan(self, seqs, strand, cooperative=1):
         b, off = L.concat(seqs)
         out = np.zeros((len(seqs), 5), dtype=np.uint32)
-        L.check(L.lib().gw_quick_scan(self._h, L.ptr(b), L.ptr(off), len(seqs), strand, L.ptr(out)))
+        L.check(L.lib().gw_quick_scan(self._h, L.ptr(b), L.ptr(off), len(seqs), strand, cooperative, L.ptr(out)))
         return out.astype(np.int64)
 
     def close(self):

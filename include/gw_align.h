@@ -158,8 +158,9 @@ int gw_gather_benchmark(const gw_index_t*, int which, uint64_t n_lookups, int it
 /* SparseSuffixArray.get (align/SparseSuffixArray.java:141-161) for n SA rows */
 int gw_locate(const gw_index_t*, int which, const uint32_t* sa_rows, uint32_t n, uint32_t* out);
 /* FMQuickScan.scanMismatchLocations (align/strategy/FMQuickScan.java:66-94) for a read batch and strand (0 '+': scans the read,
- * 1 '-': scans its complement): out n x 5 = numMismatches, longestMatch.start, longestMatch.end, si.lb, si.ub */
-int gw_quick_scan(const gw_index_t*, const char* bases, const uint64_t* offsets, uint32_t n_reads, int strand, uint32_t* out);
+ * 1 '-': scans its complement): out n x 5 = numMismatches, longestMatch.start, longestMatch.end, si.lb, si.ub.
+ * cooperative != 0: the 4-lanes-per-task kernel the aligner uses; 0: the one-thread-per-task form */
+int gw_quick_scan(const gw_index_t*, const char* bases, const uint64_t* offsets, uint32_t n_reads, int strand, int cooperative, uint32_t* out);
 /* BitParallelSmithWaterman.alignBlockDetailed(ref, query, k) (align/BitParallelSmithWaterman.java:141-147) for n pairs of ACGTN
  * strings: result[i*4..] = valid, pos, numMismatches, cigar_len ; cigars at cigar_ops[i*cigar_stride..] */
 int gw_verify_pairs(int device, const char* refs, const uint64_t* ref_off, const char* queries, const uint64_t* query_off, uint32_t n,
