@@ -11,6 +11,7 @@
 #include <map>
 #include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "sequence.hpp"
@@ -38,13 +39,26 @@ public:
     OccurrenceCountTable(const ACGTSequence* seq_, int windowSize) : seq(seq_), W(windowSize) {
         const jint numRows = (jint)((seq->textSize() + W) / W);
         occTable.assign((size_t)numRows * 5, 0);
-        for (jint i = 1; i < numRows; ++i) {
-            jlong start = (jlong)(i - 1) * W;
-            jlong end = std::min(start + W, seq->textSize());
-            jlong count[5];
-            seq->fastCountACGTN(start, end, count);
-            for (int k = 0; k < 5; ++k) occTable[(size_t)i * 5 + k] = occTable[(size_t)(i - 1) * 5 + k] + count[k];
+        // The reference fills the table with one running sum (OccurrenceCountTable.java:51-72). The per-window counts do not depend on
+        // each other, so they are taken by several threads first and summed afterwards: same table, a human-scale index opens in minutes.
+        unsigned T = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+        if (numRows < 4096) T = 1;
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < T; ++t) {
+            th.emplace_back([this, t, T, numRows]() {
+                const jint lo = 1 + (jint)((jlong)(numRows - 1) * t / T), hi = 1 + (jint)((jlong)(numRows - 1) * (t + 1) / T);
+                for (jint i = lo; i < hi; ++i) {
+                    jlong start = (jlong)(i - 1) * W;
+                    jlong end = std::min(start + W, seq->textSize());
+                    jlong count[5];
+                    seq->fastCountACGTN(start, end, count);
+                    for (int k = 0; k < 5; ++k) occTable[(size_t)i * 5 + k] = count[k];
+                }
+            });
         }
+        for (auto& x : th) x.join();
+        for (jint i = 1; i < numRows; ++i)
+            for (int k = 0; k < 5; ++k) occTable[(size_t)i * 5 + k] += occTable[(size_t)(i - 1) * 5 + k];
     }
     void getOccACGTN(jlong index, jlong occ[5]) const {
         OccCounter::lookups++;

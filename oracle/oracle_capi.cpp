@@ -212,4 +212,65 @@ int gwo_compress_roundtrip(const unsigned char* in, int n) {
     if (!snappyUncompress(c.data(), c.size(), d)) return -1;
     return d.size() == (size_t)n && memcmp(d.data(), in, (size_t)n) == 0 ? 0 : -2;
 }
+// ---- re-hosted unit-test surface (BitVectorTest, CIGARTest, SparseSuffixArrayTest, BWTransformTest) ----
+// BitVector.parseString(bits) [optionally .not() first] .lshift(len) .toString(): most significant bit first, as BitVector.toString
+// prints it (BitVector.java:73-104, :180-192, :217-224). Only the members on the alignment path (_not, _lshift) exist in the oracle.
+int gwo_bitvector_lshift(const char* bits, int len, int not_first, char* out, int cap) {
+    try {
+        const int n = (int)strlen(bits);
+        BitVector v(n);
+        for (int i = 0; i < n; ++i) if (bits[i] == '1') v.set(n - 1 - i);
+        if (not_first) v._not();
+        v._lshift(len);
+        if (cap < n + 1) return -1;
+        for (int i = 0; i < n; ++i) out[i] = ((v.block[(size_t)((n - 1 - i) / 64)] >> ((n - 1 - i) % 64)) & 1ULL) ? '1' : '0';
+        out[n] = 0;
+        return 0;
+    } catch (JavaAbort&) { return 2; }
+}
+// new CIGAR(a).add(new CIGAR(b)).toString() (CIGAR.java:121-140, :221-241); b may be empty
+int gwo_cigar_merge(const char* a, const char* b, char* out, int cap) {
+    CIGAR c1{std::string(a)};
+    CIGAR c2{std::string(b)};
+    c1.add(c2);
+    const std::string s = c1.toString();
+    if ((int)s.size() + 1 > cap) return -1;
+    memcpy(out, s.c_str(), s.size() + 1);
+    return (int)c1.cigar.size();
+}
+// new CIGAR() with add(length, type) calls
+int gwo_cigar_build(const int* lengths, const char* types, int n, char* out, int cap) {
+    CIGAR c;
+    for (int i = 0; i < n; ++i) c.add(lengths[i], types[i]);
+    const std::string s = c.toString();
+    if ((int)s.size() + 1 > cap) return -1;
+    memcpy(out, s.c_str(), s.size() + 1);
+    return (int)c.cigar.size();
+}
+// SparseSuffixArray.buildFromSuffixArray(CyclicSAIS(seq), L).saveTo -> loadFrom (SparseSuffixArray.java:91-131): 0 when the reloaded
+// samples equal SA[i * L]; sa_out receives the suffix array
+int gwo_ssa_roundtrip(const char* seq, int L, const char* tmp_path, int* sa_out) {
+    try {
+        ACGTSequence s{std::string(seq)};
+        std::vector<uint32_t> codes((size_t)s.textSize());
+        for (jlong i = 0; i < s.textSize(); ++i) codes[(size_t)i] = (uint32_t)s.lookup(i);
+        std::vector<uint32_t> SA = cyclicSuffixSort(codes);
+        for (size_t i = 0; i < SA.size(); ++i) sa_out[i] = (int)SA[i];
+        SparseSuffixArray a = SparseSuffixArray::buildFromSuffixArray(SA, L);
+        saveSSA(a, tmp_path);
+        SparseSuffixArray b = loadSSA(tmp_path);
+        if (b.N != a.N || b.L != a.L || b.sparseSA.size() != a.sparseSA.size()) return 1;
+        for (size_t i = 0; i < a.sparseSA.size(); ++i) if (a.sparseSA[i] != b.sparseSA[i] || a.sparseSA[i] != SA[i * (size_t)L]) return 2;
+        return 0;
+    } catch (std::exception& e) { g_err = e.what(); return -1; }
+}
+// ACGTSequence.loadFrom(path).toString() (BWTransformTest.transform reads .f.3bit / .r.3bit back)
+char* gwo_load_acgt_string(const char* path) {
+    try {
+        std::string s = loadACGTSequence(path).toString();
+        char* o = (char*)malloc(s.size() + 1);
+        memcpy(o, s.c_str(), s.size() + 1);
+        return o;
+    } catch (std::exception& e) { g_err = e.what(); return nullptr; }
+}
 }  // extern "C"

@@ -53,6 +53,12 @@ def lib():
         L.gwo_query_mask64.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
         L.gwo_staircase_table.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_ulonglong), C.c_int]
         L.gwo_compress_roundtrip.argtypes = [C.c_char_p, C.c_int]
+        L.gwo_bitvector_lshift.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_char_p, C.c_int]
+        L.gwo_cigar_merge.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]
+        L.gwo_cigar_build.argtypes = [C.POINTER(C.c_int), C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+        L.gwo_ssa_roundtrip.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.POINTER(C.c_int)]
+        L.gwo_load_acgt_string.restype = C.c_void_p
+        L.gwo_load_acgt_string.argtypes = [C.c_char_p]
         _lib = L
     return _lib
 
