@@ -220,6 +220,25 @@ GW_HD const u64* gw_lane_staircase(const GwSearchEnv& env, const GwSlab& s, GwLa
     return env.sf.words + ln.sf_off;
 }
 
+GW_HD void gw_prefetch(const void* p) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#else
+    (void)p;
+#endif
+}
+// what the next poll of this read will touch is known as soon as a slice ends: the root of the queue names the state, and a sift-down
+// starts in the first entries of the queue. Both lines are requested now, a whole trip of the warp ahead of their use.
+template <int MAXH>
+GW_HD void gw_lane_prefetch_next(const GwSlab& s, const GwLane<MAXH>& ln) {
+    if (ln.qn > 0 && ln.mid == 0) {
+        if (ln.root_off != ln.cached) gw_prefetch(s.at(ln.root_off));
+        if (ln.qn > 1) gw_prefetch(s.queue() + 1);
+    }
+}
+template <int MAXH>
+GW_HD bool gw_lane_is_exclusive(const GwLane<MAXH>& ln) { return ln.c_off == ln.base && ln.C.next_split < 0; }
+
 template <int MAXH>
 GW_HD int gw_lane_poll(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln) {
     GwReadCtx* c = s.ctx();
@@ -267,13 +286,16 @@ GW_HD int gw_lane_poll(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln
 // FMIndexOnGenome.bidirectionalSearch (two rank queries on one index, FMIndexOnGenome.java:148-194), ReadAlignmentNFA.nextState +
 // SearchState.nextState (ReadAlignmentNFA.java:146-215), queue insertion. MAXH: compile-time bound of the NFA height (k + 1): for
 // MAXH <= 8 the rows stay in registers (every loop over rows is unrolled with constant indices).
-template <int MAXH>
+// EXCL: the caller knows that the state heads no split chain and is the polled queue entry itself (nine steps out of ten): the code
+// for chains (flags written back to the arena, insertion through the chain's head) is then not even compiled in, and a warp that runs
+// such states only never passes through it.
+template <int MAXH, bool EXCL = false>
 GW_HD int gw_lane_try(const GwSearchEnv& env, const GwSlab& s, GwLane<MAXH>& ln) {
     GwReadCtx* c = s.ctx();
     const GwDevConfig& cfg = env.cfg;
     const GwIndexView& ix = env.ix;
     GwState& C = ln.C;
-    const bool exclusive = ln.c_off == ln.base && C.next_split < 0;
+    const bool exclusive = EXCL || (ln.c_off == ln.base && C.next_split < 0);
     const int strand = gw_strand(&C);
     const int dir = gw_dir(&C);
     const bool fwdC = dir != GW_DIR_B;

@@ -134,6 +134,7 @@ static_assert(GW_REC_WORDS(4) % 2 == 1 && GW_REC_WORDS(8) % 2 == 1 && GW_REC_WOR
 #define GW_RS_FREE 0u
 #define GW_RS_HOT 1u     // in the best-first loop: wants search slices
 #define GW_RS_COLD 2u    // waits for an out-of-line continuation (ln.mid == GW_MID_SPLIT / GW_MID_REPORT)
+#define GW_RS_CHAIN 3u   // mid step on a fragment of a split chain (one step in ten): extended by the general form of the slice
 
 // dynamic shared memory of a CTA, per warp: ready FIFO, fragment FIFO, record states (64 words), selection scratch (32 words), records
 extern __shared__ uint32_t gw_flow_smem[];
@@ -176,18 +177,19 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, MINB) gw_flow_kernel(GwSearch
     GwRec<MAXH>* recs = reinterpret_cast<GwRec<MAXH>*>(sel + 32);
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_cold = 0, owned = 0, trip = 0, stuck = 0;
+    uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_cold = 0, age_chain = 0, owned = 0, trip = 0, stuck = 0;
     bool drained = false;
     rstate[lane] = GW_RS_FREE; rstate[lane + 32u] = GW_RS_FREE;
     __syncwarp();
     for (;;) {
         ++trip;
-        uint32_t n_hot, n_cold, n_free;
+        uint32_t n_hot, n_cold, n_chain, n_free;
         {
-            const uint32_t s0 = lane < RW ? rstate[lane] : 3u, s1 = lane + 32u < RW ? rstate[lane + 32u] : 3u;
+            const uint32_t s0 = lane < RW ? rstate[lane] : 9u, s1 = lane + 32u < RW ? rstate[lane + 32u] : 9u;
             n_hot = (uint32_t)__popc(__ballot_sync(FULL, s0 == GW_RS_HOT)) + (uint32_t)__popc(__ballot_sync(FULL, s1 == GW_RS_HOT));
             n_cold = (uint32_t)__popc(__ballot_sync(FULL, s0 == GW_RS_COLD)) + (uint32_t)__popc(__ballot_sync(FULL, s1 == GW_RS_COLD));
-            n_free = (uint32_t)RW - n_hot - n_cold;
+            n_chain = (uint32_t)__popc(__ballot_sync(FULL, s0 == GW_RS_CHAIN)) + (uint32_t)__popc(__ballot_sync(FULL, s1 == GW_RS_CHAIN));
+            n_free = (uint32_t)RW - n_hot - n_cold - n_chain;
         }
         const uint32_t n_ready = r_tail - r_head, n_fr = f_tail - f_head;
         // ---- verification batch
@@ -215,10 +217,9 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, MINB) gw_flow_kernel(GwSearch
                     dp = gw_job_begin_dp(env, sv, &job, (int)(id & 1u), my_hist, stride);
                 }
                 const int hint = (int)__reduce_max_sync(FULL, dp ? (unsigned)job.dp.bmax : 0u);
-                if (dp) {
-                    gw_job_columns(env, &job, job.dp.ncols, my_hist, stride, hint);
-                    gw_job_trace(sv, &job, my_hist, stride);
-                }
+                if (dp) gw_job_columns(env, &job, job.dp.ncols, my_hist, stride, hint);
+                __syncwarp();
+                if (dp) gw_job_trace(sv, &job, my_hist, stride);
             }
             __syncwarp();
             const uint32_t nid = __shfl_down_sync(FULL, id, 1);
@@ -271,7 +272,7 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, MINB) gw_flow_kernel(GwSearch
                 continue;
             }
         }
-        if (n_hot == 0u && n_cold == 0u) {
+        if (n_hot == 0u && n_cold == 0u && n_chain == 0u) {
             if (n_fr == 0u && n_ready == 0u && drained) break;
             ++stuck;   // nothing searches and nothing could be taken up: the waiting fragments are verified whatever their number
             continue;
@@ -279,7 +280,18 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, MINB) gw_flow_kernel(GwSearch
         int r = GW_STEP_CONTINUE;
         int mine = -1;
         // ---- deferred continuations, for many records at once
-        if (n_cold != 0u && (n_cold >= pp.batch || n_hot == 0u || ++age_cold >= pp.age)) {
+        if (n_chain != 0u && (n_chain >= pp.batch || n_hot == 0u || ++age_chain >= pp.age)) {
+            // ---- steps on fragments of split chains, for many records at once (general form of the extension)
+            age_chain = 0;
+            gw_flow_select<RW>(rstate, sel, GW_RS_CHAIN, lane, lt, (trip & 1u) != 0u, &mine);
+            if (mine >= 0) {
+                GwRec<MAXH>& rc = recs[mine];
+                const GwSlab s = rc.slab();
+                r = gw_lane_try<MAXH, false>(env, s, rc.ln);
+                if (r == GW_STEP_CONTINUE && rc.ln.mid != GW_MID_TRY) rstate[mine] = rc.ln.mid >= GW_MID_SPLIT ? GW_RS_COLD : GW_RS_HOT;
+                if (r == GW_STEP_CONTINUE) gw_lane_prefetch_next(s, rc.ln);
+            }
+        } else if (n_cold != 0u && (n_cold >= pp.batch || n_hot == 0u || ++age_cold >= pp.age)) {
             age_cold = 0;
             gw_flow_select<RW>(rstate, sel, GW_RS_COLD, lane, lt, (trip & 1u) != 0u, &mine);
             if (mine >= 0) {
@@ -313,11 +325,20 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, MINB) gw_flow_kernel(GwSearch
                     if (nb) { gw_promote_commit(s, nb, const_cast<u64**>(slabs) + rc->slot); rc->set_slab(s, rc->slot); }
                 }
             }
-            if (mine >= 0) {
-                GwLane<MAXH>& ln = rc->ln;
-                if (ln.mid == 0) r = gw_lane_poll(env, s, ln);
-                if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY) r = gw_lane_try(env, s, ln);
-                if (r == GW_STEP_CONTINUE && ln.mid >= GW_MID_SPLIT) rstate[mine] = GW_RS_COLD;
+            // The lanes are brought together again before each part (the compiler lets a lane that skips the poll run ahead into the
+            // extension on its own, and the warp would then pass through the same code twice with half of its lanes each time)
+            GwLane<MAXH>& ln = rc->ln;
+            __syncwarp();
+            if (mine >= 0 && ln.mid == 0) {
+                r = gw_lane_poll(env, s, ln);
+                if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY && !gw_lane_is_exclusive(ln)) rstate[mine] = GW_RS_CHAIN;   // one of the rare steps on a split chain
+            }
+            __syncwarp();
+            if (mine >= 0 && r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY && rstate[mine] == GW_RS_HOT) r = gw_lane_try<MAXH, true>(env, s, ln);
+            __syncwarp();
+            if (mine >= 0 && r == GW_STEP_CONTINUE) {
+                if (ln.mid >= GW_MID_SPLIT) rstate[mine] = GW_RS_COLD;
+                gw_lane_prefetch_next(s, ln);
             }
         }
         // ---- parked reads queue their fragments (both fragments of a read next to each other); finished reads just leave
@@ -553,7 +574,7 @@ static void gw_flow_attr() {
     cudaFuncSetAttribute(gw_flow_kernel<MAXH, MINB, RW>, cudaFuncAttributePreferredSharedMemoryCarveout, pct > 100 ? 100 : pct);
 }
 void gwk_flow_setup(void) {   // function attributes are per device: called once per aligner (after cudaSetDevice)
-    gw_flow_attr<4, 2, 48>(); gw_flow_attr<4, 2, 40>(); gw_flow_attr<8, 2, 40>(); gw_flow_attr<GW_MAX_ROWS, 2, 24>();
+    gw_flow_attr<4, 2, 48>(); gw_flow_attr<4, 2, 40>(); gw_flow_attr<4, 2, 32>(); gw_flow_attr<8, 2, 40>(); gw_flow_attr<GW_MAX_ROWS, 2, 24>();
 }
 void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
               uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh, int records) {
@@ -563,7 +584,7 @@ void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const 
     pp.batch = batch < 1 ? 1 : batch; pp.age = age < 1 ? 1 : age; pp.flush = flush < 1 ? 1 : flush;
     GwU64x2* h = (GwU64x2*)hist;
 #define GW_FLOW_LAUNCH(H, B, R) gw_flow_kernel<H, B, R><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<H, R>(), st>>>(env, slabs, active, n_active, work_counter, h, pp)
-    if (maxh <= 4) { if (records >= 48) GW_FLOW_LAUNCH(4, 2, 48); else GW_FLOW_LAUNCH(4, 2, 40); }
+    if (maxh <= 4) { if (records >= 48) GW_FLOW_LAUNCH(4, 2, 48); else if (records >= 40) GW_FLOW_LAUNCH(4, 2, 40); else GW_FLOW_LAUNCH(4, 2, 32); }
     else if (maxh <= 8) GW_FLOW_LAUNCH(8, 2, 40);
     else GW_FLOW_LAUNCH(GW_MAX_ROWS, 2, 24);
 #undef GW_FLOW_LAUNCH

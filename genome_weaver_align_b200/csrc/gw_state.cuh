@@ -75,7 +75,8 @@ struct GwSlab {
     // insertion) next to the state offset, so that a sift step is ONE 128-bit load per level
     GW_HD GwQEntry* queue() const { return reinterpret_cast<GwQEntry*>(base + GW_QUEUE_BASE); }
     GW_HD int32_t* hits() const { return reinterpret_cast<int32_t*>(base + GW_QUEUE_BASE + 2u * sp.queue_cap); }
-    GW_HD uint32_t arena_begin() const { return (GW_QUEUE_BASE + 2u * sp.queue_cap + (sp.hit_cap + 1) / 2 + 1u) & ~1u; }
+    // 128-byte aligned: a state of a read with k <= 3 (16 words) is exactly one line
+    GW_HD uint32_t arena_begin() const { return (GW_QUEUE_BASE + 2u * sp.queue_cap + (sp.hit_cap + 1) / 2 + 15u) & ~15u; }
     GW_HD u64* at(int32_t off) const { return base + off; }
 };
 

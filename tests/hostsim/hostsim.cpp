@@ -139,7 +139,8 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
                     if (nocache && ln.mid == 0) ln.cached = -1;
                     if (spill && ++slices % spill == 0) { gw_lane_flush(s, ln); gw_lane_reload(s, ln); }
                     if (ln.mid == 0) r = gw_lane_poll(env, s, ln);
-                    if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY) r = gw_lane_try(env, s, ln);
+                    if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY)   // as the flow kernel: the specialised form for states that head no split chain
+                        r = gw_lane_is_exclusive(ln) ? gw_lane_try<MAXH, true>(env, s, ln) : gw_lane_try<MAXH, false>(env, s, ln);
                     if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_SPLIT) r = gw_lane_split(env, s, ln);
                     if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_REPORT) r = gw_lane_report(env, s, ln);
                 }
