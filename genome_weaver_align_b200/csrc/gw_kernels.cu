@@ -83,20 +83,17 @@ __global__ void __launch_bounds__(256) gw_scan_coop_kernel(GwIndexView ix, u64* 
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Flow kernel: warp-level pools without rounds. Every warp owns, in shared memory,
-//   * a pool of RW search records (GwLane + the read's work area), more than it has lanes: a record is a read that is in the
-//     best-first loop; records are not tied to lanes,
-//   * two small FIFOs: reads ready to be taken up (again), and fragments waiting for locate + verification,
-// and loops over kinds of warp-wide work, each on up to 32 items of the SAME kind, so that the lanes that execute an instruction
-// together all have work of that kind (a read that parks, finishes or waits for a rare continuation does not leave a lane idle):
-//   * a search slice: the lanes take the records that can search — one poll + one candidate extension each (gw_lane_poll / _try),
-//   * the rare, long continuations of a step (split + soft-clip children, chain reporting) once `batch` records wait for one (or
-//     `age` trips passed, or nothing else can run),
-//   * pick-up: free records take reads from the ready FIFO (refilled from the global work list, `cap` reads at a time): the read's
-//     verification results are consumed, or its queue is seeded, and the record starts searching,
-//   * a verification batch as soon as 32 fragments wait: every lane locates one fragment and runs its DP + traceback; the reads
-//     whose fragments are all done go back to the ready FIFO.
-// There is no per-round tail, and locate / DP always run with (nearly) full warps.
+// Flow kernel: warp-level pools without rounds. Every warp owns two small FIFOs in shared memory — reads ready to (re)start
+// searching and fragments waiting for locate + verification — and loops over three kinds of warp-wide work:
+//   * search slices: one poll + one candidate extension per lane and trip, on the lane's register copy of its read (GwLane); the
+//     long, rarely taken continuations (taking a read up / consuming verification results, split + soft-clip children, chain
+//     reporting) are deferred until `batch` lanes wait for one (or `age` trips passed, or nothing else can run), so that they run
+//     for several lanes at once instead of one lane while 31 wait,
+//   * pick-up: idle lanes take reads from the ready FIFO (refilled from the global work list, `cap` reads at a time),
+//   * a verification batch as soon as 32 fragments wait: every lane walks one fragment to its SA sample and runs its DP + traceback;
+//     the reads whose fragments are all done go back to the ready FIFO.
+// There is no per-round tail: a lane that parks or finishes a read takes the next one at once, and locate / DP always run with
+// (nearly) full warps.
 #ifndef GW_FLOW_THREADS
 #define GW_FLOW_THREADS 256
 #endif
@@ -105,96 +102,39 @@ __global__ void __launch_bounds__(256) gw_scan_coop_kernel(GwIndexView ix, u64* 
 
 struct GwFlowParams {
     uint32_t cap;        // reads a warp takes from the work list at a time
-    uint32_t batch;      // records that must wait for a deferred continuation before the warp runs it
-    uint32_t age;        // ... or this many trips since the first one started waiting
-    uint32_t flush;      // once the work list is drained, a partial verification batch runs when fewer than this many records search
+    uint32_t batch;      // lanes that must wait for a deferred continuation before the warp runs it
+    uint32_t age;        // ... or this many trips since the first lane started waiting
+    uint32_t flush;      // once the work list is drained, a partial verification batch runs when this many lanes idle
 };
 
-// a search record: the lane record of gw_search.cuh + where the read's work area is. All members are 32-bit and the size is an odd
-// number of words, so records at consecutive indices never share a bank.
-template <int MAXH>
-struct GwRec {
-    GwLane<MAXH> ln;
-    uint32_t slab_lo, slab_hi;   // work area of the read
-    uint32_t slab_words, queue_cap, hit_cap;
-    uint32_t slot;
-    __device__ __forceinline__ GwSlab slab() const {
-        GwSlabParams sp; sp.slab_words = slab_words; sp.queue_cap = queue_cap; sp.hit_cap = hit_cap;
-        return GwSlab(reinterpret_cast<u64*>((unsigned long long)slab_lo | ((unsigned long long)slab_hi << 32)), sp);
-    }
-    __device__ __forceinline__ void set_slab(const GwSlab& s, uint32_t slot_) {
-        const unsigned long long b = (unsigned long long)s.base;
-        slab_lo = (uint32_t)b; slab_hi = (uint32_t)(b >> 32);
-        slab_words = s.sp.slab_words; queue_cap = s.sp.queue_cap; hit_cap = s.sp.hit_cap; slot = slot_;
-    }
-};
-#define GW_REC_WORDS(MAXH) ((uint32_t)(sizeof(GwRec<MAXH>) / 4))
-static_assert(GW_REC_WORDS(4) % 2 == 1 && GW_REC_WORDS(8) % 2 == 1 && GW_REC_WORDS(GW_MAX_ROWS) % 2 == 1, "odd word stride");
-
-#define GW_RS_FREE 0u
-#define GW_RS_HOT 1u     // in the best-first loop: wants search slices
-#define GW_RS_COLD 2u    // waits for an out-of-line continuation (ln.mid == GW_MID_SPLIT / GW_MID_REPORT)
-#define GW_RS_CHAIN 3u   // mid step on a fragment of a split chain (one step in ten): extended by the general form of the slice
-
-// dynamic shared memory of a CTA, per warp: ready FIFO, fragment FIFO, record states (64 words), selection scratch (32 words), records
+// dynamic shared memory of a CTA: the two FIFOs of every warp, then one GwLane record per thread (odd word stride)
 extern __shared__ uint32_t gw_flow_smem[];
-#define GW_FLOW_WARP_WORDS(MAXH, RW) (2u * GW_RING + 64u + 32u + (uint32_t)(RW) * GW_REC_WORDS(MAXH))
-template <int MAXH, int RW>
-static size_t gw_flow_smem_bytes() { return (size_t)GW_FLOW_WARP_WORDS(MAXH, RW) * GW_WARPS * 4; }
+template <int MAXH>
+static size_t gw_flow_smem_bytes() { return ((size_t)2 * GW_WARPS * GW_RING + (size_t)GW_FLOW_THREADS * GW_LANE_WORDS(MAXH)) * 4; }
 
-// the warp's records in state `kind`: up to 32 of them are handed to the lanes (lane i gets the i-th; -1: none). `flip` alternates
-// which half of the pool is served first, so that no record waits for ever behind the others. Returns how many there are.
-template <int RW>
-__device__ __forceinline__ uint32_t gw_flow_select(const uint32_t* rstate, uint32_t* sel, uint32_t kind, uint32_t lane, uint32_t lt, bool flip, int* mine) {
-    const uint32_t FULL = 0xFFFFFFFFu;
-    const bool a0 = lane < RW && rstate[lane] == kind, a1 = lane + 32u < RW && rstate[lane + 32u] == kind;
-    uint32_t b0 = __ballot_sync(FULL, a0), b1 = __ballot_sync(FULL, a1);
-    const uint32_t n = (uint32_t)__popc(b0) + (uint32_t)__popc(b1);
-    if (n == 0u) { *mine = -1; return 0u; }
-    const uint32_t first = flip ? b1 : b0, second = flip ? b0 : b1;
-    const bool af = flip ? a1 : a0, as = flip ? a0 : a1;
-    const uint32_t base_f = flip ? 32u : 0u, base_s = flip ? 0u : 32u;
-    if (af) { const uint32_t r = (uint32_t)__popc(first & lt); sel[r] = base_f + lane; }
-    if (as) { const uint32_t r = (uint32_t)__popc(first) + (uint32_t)__popc(second & lt); if (r < 32u) sel[r] = base_s + lane; }
-    __syncwarp();
-    *mine = lane < n ? (int)sel[lane] : -1;
-    __syncwarp();
-    return n;
-}
-
-// MINB: CTAs per SM the kernel is compiled for (register cap 65536 / (MINB * 256)); RW: search records per warp (32 < RW <= 64)
-template <int MAXH, int MINB, int RW>
-__global__ void __launch_bounds__(GW_FLOW_THREADS, MINB) gw_flow_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
+template <int MAXH>
+__global__ void __launch_bounds__(GW_FLOW_THREADS, 2) gw_flow_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
                                                                   uint32_t* work_counter, GwU64x2* hist, GwFlowParams pp) {
     const uint32_t FULL = 0xFFFFFFFFu, MASK = GW_RING - 1u;
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
-    uint32_t* wbase = gw_flow_smem + wid * GW_FLOW_WARP_WORDS(MAXH, RW);
-    uint32_t* ready = wbase;
-    uint32_t* frags = wbase + GW_RING;
-    uint32_t* rstate = wbase + 2 * GW_RING;
-    uint32_t* sel = rstate + 64;
-    GwRec<MAXH>* recs = reinterpret_cast<GwRec<MAXH>*>(sel + 32);
+    uint32_t* ready = gw_flow_smem + wid * GW_RING;
+    uint32_t* frags = gw_flow_smem + (GW_WARPS + wid) * GW_RING;
+    GwLane<MAXH>& ln = *reinterpret_cast<GwLane<MAXH>*>(gw_flow_smem + 2 * GW_WARPS * GW_RING + threadIdx.x * GW_LANE_WORDS(MAXH));
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_cold = 0, age_chain = 0, owned = 0, trip = 0, stuck = 0;
+    uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_pick = 0, age_cold = 0, owned = 0;
     bool drained = false;
-    rstate[lane] = GW_RS_FREE; rstate[lane + 32u] = GW_RS_FREE;
-    __syncwarp();
+    bool have = false;
+    GwSlab s;
+    ln.mid = 0; ln.top = 0; ln.k = 0;
+    uint32_t slot = 0;
     for (;;) {
-        ++trip;
-        uint32_t n_hot, n_cold, n_chain, n_free;
-        {
-            const uint32_t s0 = lane < RW ? rstate[lane] : 9u, s1 = lane + 32u < RW ? rstate[lane + 32u] : 9u;
-            n_hot = (uint32_t)__popc(__ballot_sync(FULL, s0 == GW_RS_HOT)) + (uint32_t)__popc(__ballot_sync(FULL, s1 == GW_RS_HOT));
-            n_cold = (uint32_t)__popc(__ballot_sync(FULL, s0 == GW_RS_COLD)) + (uint32_t)__popc(__ballot_sync(FULL, s1 == GW_RS_COLD));
-            n_chain = (uint32_t)__popc(__ballot_sync(FULL, s0 == GW_RS_CHAIN)) + (uint32_t)__popc(__ballot_sync(FULL, s1 == GW_RS_CHAIN));
-            n_free = (uint32_t)RW - n_hot - n_cold - n_chain;
-        }
+        const uint32_t busy = __ballot_sync(FULL, have);
+        const uint32_t idle = ~busy;
         const uint32_t n_ready = r_tail - r_head, n_fr = f_tail - f_head;
         // ---- verification batch
-        if (n_fr >= 32u || (n_fr != 0u && ((n_ready == 0u && drained && n_hot < pp.flush) || stuck != 0u))) {
-            stuck = 0;
+        if (n_fr >= 32u || (n_fr != 0u && n_ready == 0u && drained && (busy == 0u || (uint32_t)__popc(idle) >= pp.flush))) {
             uint32_t nb = n_fr < 32u ? n_fr : 32u;
             if (n_fr > 32u && (frags[(f_head + 31u) & MASK] >> 1) == (frags[(f_head + 32u) & MASK] >> 1)) nb = 31u;   // both fragments of a read in one batch
             const uint32_t id = lane < nb ? frags[(f_head + lane) & MASK] : 0xFFFFFFFFu;
@@ -230,40 +170,34 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, MINB) gw_flow_kernel(GwSearch
             __syncwarp();
             continue;
         }
-        // ---- pick-up: free records take reads from the ready FIFO (refilled from the global work list). Taking a read up is long,
-        // rarely shared code, so it is done for many reads at once: when few records can search, or many are free
-        if (n_free != 0u && (n_ready != 0u || !drained) && (n_hot < 32u || n_free >= 24u)) {
-            uint32_t nrd = n_ready;
-            const uint32_t want = n_free < 32u ? n_free : 32u;
-            if (nrd < want && !drained && owned + pp.cap <= GW_RING) {
-                uint32_t first = 0;
-                if (lane == 0) first = atomicAdd(work_counter, pp.cap);
-                first = __shfl_sync(FULL, first, 0);
-                uint32_t got = 0;
-                if (first < n_active) got = min(pp.cap, n_active - first);
-                if (first + pp.cap >= n_active) drained = true;
-                if (lane < got) ready[(r_tail + lane) & MASK] = active ? active[first + lane] : first + lane;
-                r_tail += got; nrd += got; owned += got;
-                __syncwarp();
-            }
-            const uint32_t take = nrd < want ? nrd : want;
-            if (take != 0u) {
-                int mine;
-                gw_flow_select<RW>(rstate, sel, GW_RS_FREE, lane, lt, false, &mine);
+        // ---- pick-up (idle lanes take reads from the ready FIFO; refill from the global work list)
+        if (idle != 0u && (n_ready != 0u || !drained)) {
+            if ((uint32_t)__popc(idle) >= pp.batch || busy == 0u || ++age_pick >= pp.age) {
+                age_pick = 0;
+                uint32_t nrd = n_ready;
+                if (nrd < (uint32_t)__popc(idle) && !drained && owned + pp.cap <= GW_RING) {
+                    uint32_t first = 0;
+                    if (lane == 0) first = atomicAdd(work_counter, pp.cap);
+                    first = __shfl_sync(FULL, first, 0);
+                    uint32_t got = 0;
+                    if (first < n_active) got = min(pp.cap, n_active - first);
+                    if (first + pp.cap >= n_active) drained = true;
+                    if (lane < got) ready[(r_tail + lane) & MASK] = active ? active[first + lane] : first + lane;
+                    r_tail += got; nrd += got; owned += got;
+                    __syncwarp();
+                }
                 int r0 = -1;
-                uint32_t slot = 0;
-                if (lane < take) {
-                    slot = ready[(r_head + lane) & MASK];
-                    const GwSlab s(slabs[slot]);
-                    r0 = gw_resume_read(env, s);
-                    if (r0 == GW_STEP_CONTINUE) {
-                        GwRec<MAXH>& rc = recs[mine];
-                        rc.set_slab(s, slot);
-                        gw_lane_load(s, rc.ln);
-                        rstate[mine] = GW_RS_HOT;
+                if (!have) {
+                    const uint32_t i = (uint32_t)__popc(idle & lt);
+                    if (i < nrd) {
+                        slot = ready[(r_head + i) & MASK];
+                        s = GwSlab(slabs[slot]);
+                        r0 = gw_resume_read(env, s);
+                        have = r0 == GW_STEP_CONTINUE;
+                        if (have) gw_lane_load(s, ln);
                     }
                 }
-                r_head += take;
+                r_head += min((uint32_t)__popc(idle), nrd);
                 const uint32_t pk = __ballot_sync(FULL, r0 == GW_STEP_PARKED);   // exact hit: needs its locate only
                 if (r0 == GW_STEP_PARKED) frags[(f_tail + (uint32_t)__popc(pk & lt)) & MASK] = slot * 2u;
                 f_tail += (uint32_t)__popc(pk);
@@ -271,85 +205,53 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, MINB) gw_flow_kernel(GwSearch
                 __syncwarp();
                 continue;
             }
-        }
-        if (n_hot == 0u && n_cold == 0u && n_chain == 0u) {
+        } else if (busy == 0u) {
             if (n_fr == 0u && n_ready == 0u && drained) break;
-            ++stuck;   // nothing searches and nothing could be taken up: the waiting fragments are verified whatever their number
-            continue;
         }
+        // ---- one search slice per lane
         int r = GW_STEP_CONTINUE;
-        int mine = -1;
-        // ---- deferred continuations, for many records at once
-        if (n_chain != 0u && (n_chain >= pp.batch || n_hot == 0u || ++age_chain >= pp.age)) {
-            // ---- steps on fragments of split chains, for many records at once (general form of the extension)
-            age_chain = 0;
-            gw_flow_select<RW>(rstate, sel, GW_RS_CHAIN, lane, lt, (trip & 1u) != 0u, &mine);
-            if (mine >= 0) {
-                GwRec<MAXH>& rc = recs[mine];
-                const GwSlab s = rc.slab();
-                r = gw_lane_try<MAXH, false>(env, s, rc.ln);
-                if (r == GW_STEP_CONTINUE && rc.ln.mid != GW_MID_TRY) rstate[mine] = rc.ln.mid >= GW_MID_SPLIT ? GW_RS_COLD : GW_RS_HOT;
-                if (r == GW_STEP_CONTINUE) gw_lane_prefetch_next(s, rc.ln);
-            }
-        } else if (n_cold != 0u && (n_cold >= pp.batch || n_hot == 0u || ++age_cold >= pp.age)) {
-            age_cold = 0;
-            gw_flow_select<RW>(rstate, sel, GW_RS_COLD, lane, lt, (trip & 1u) != 0u, &mine);
-            if (mine >= 0) {
-                GwRec<MAXH>& rc = recs[mine];
-                const GwSlab s = rc.slab();
-                r = rc.ln.mid == GW_MID_SPLIT ? gw_lane_split(env, s, rc.ln) : gw_lane_report(env, s, rc.ln);
-                if (r == GW_STEP_CONTINUE) rstate[mine] = GW_RS_HOT;
-            }
-        } else {
-            // ---- one search slice for up to 32 records
-            gw_flow_select<RW>(rstate, sel, GW_RS_HOT, lane, lt, (trip & 1u) != 0u, &mine);
-            GwRec<MAXH>* rc = mine >= 0 ? &recs[mine] : &recs[0];
-            GwSlab s;
-            if (mine >= 0) s = rc->slab();
-            {   // work areas that are nearly full: the reads go on in a larger one; the lanes of the warp share each copy
-                const bool wantp = mine >= 0 && rc->ln.mid == 0 && gw_wants_promotion(s, (uint32_t)rc->ln.top, rc->ln.k);
-                if (__ballot_sync(FULL, wantp) != 0u) {
-                    if (wantp) gw_lane_flush(s, rc->ln);   // the copy takes the work area as it is in HBM
-                    u64* nb = wantp ? gw_promote_take(s) : nullptr;
-                    uint32_t pm = __ballot_sync(FULL, nb != nullptr);
-                    const uint32_t my_top = nb ? (uint32_t)rc->ln.top : 0u;
-                    while (pm) {
-                        const int src = __ffs(pm) - 1;
-                        pm &= pm - 1u;
-                        const u64* from = reinterpret_cast<const u64*>(__shfl_sync(FULL, (unsigned long long)s.base, src));
-                        u64* to = reinterpret_cast<u64*>(__shfl_sync(FULL, (unsigned long long)nb, src));
-                        const uint32_t top = __shfl_sync(FULL, my_top, src);
-                        gw_promote_copy(from, to, top, lane, 32u);
-                    }
-                    __syncwarp();
-                    if (nb) { gw_promote_commit(s, nb, const_cast<u64**>(slabs) + rc->slot); rc->set_slab(s, rc->slot); }
+        {   // work areas that are nearly full: the reads go on in a larger one; the lanes of the warp share each copy
+            const bool wantp = have && ln.mid == 0 && gw_wants_promotion(s, (uint32_t)ln.top, ln.k);
+            if (__ballot_sync(FULL, wantp) != 0u) {
+                if (wantp) gw_lane_flush(s, ln);   // the copy takes the work area as it is in HBM
+                u64* nb = wantp ? gw_promote_take(s) : nullptr;
+                uint32_t pm = __ballot_sync(FULL, nb != nullptr);
+                const uint32_t my_top = nb ? (uint32_t)ln.top : 0u;
+                while (pm) {
+                    const int src = __ffs(pm) - 1;
+                    pm &= pm - 1u;
+                    const u64* from = reinterpret_cast<const u64*>(__shfl_sync(FULL, (unsigned long long)s.base, src));
+                    u64* to = reinterpret_cast<u64*>(__shfl_sync(FULL, (unsigned long long)nb, src));
+                    const uint32_t top = __shfl_sync(FULL, my_top, src);
+                    gw_promote_copy(from, to, top, lane, 32u);
                 }
+                __syncwarp();
+                if (nb) gw_promote_commit(s, nb, const_cast<u64**>(slabs) + slot);
             }
-            // The lanes are brought together again before each part (the compiler lets a lane that skips the poll run ahead into the
-            // extension on its own, and the warp would then pass through the same code twice with half of its lanes each time)
-            GwLane<MAXH>& ln = rc->ln;
-            __syncwarp();
-            if (mine >= 0 && ln.mid == 0) {
-                r = gw_lane_poll(env, s, ln);
-                if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY && !gw_lane_is_exclusive(ln)) rstate[mine] = GW_RS_CHAIN;   // one of the rare steps on a split chain
-            }
-            __syncwarp();
-            if (mine >= 0 && r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY && rstate[mine] == GW_RS_HOT) r = gw_lane_try<MAXH, true>(env, s, ln);
-            __syncwarp();
-            if (mine >= 0 && r == GW_STEP_CONTINUE) {
-                if (ln.mid >= GW_MID_SPLIT) rstate[mine] = GW_RS_COLD;
-                gw_lane_prefetch_next(s, ln);
+        }
+        // the lanes are brought together before each part: the compiler lets a lane that skips the poll run ahead into the extension
+        // on its own, and the warp would then pass through the same code twice with part of its lanes each time
+        __syncwarp();
+        if (have && ln.mid == 0) r = gw_lane_poll(env, s, ln);
+        __syncwarp();
+        if (have && r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY) r = gw_lane_try<MAXH, false>(env, s, ln);
+        __syncwarp();
+        // ---- deferred continuations
+        {
+            const bool wants = have && r == GW_STEP_CONTINUE && ln.mid >= GW_MID_SPLIT;
+            const uint32_t cold = __ballot_sync(FULL, wants);
+            if (cold != 0u) {
+                const uint32_t hot = __ballot_sync(FULL, have && r == GW_STEP_CONTINUE && ln.mid < GW_MID_SPLIT);
+                if ((uint32_t)__popc(cold) >= pp.batch || hot == 0u || ++age_cold >= pp.age) {
+                    age_cold = 0;
+                    if (wants) r = ln.mid == GW_MID_SPLIT ? gw_lane_split(env, s, ln) : gw_lane_report(env, s, ln);
+                }
             }
         }
         // ---- parked reads queue their fragments (both fragments of a read next to each other); finished reads just leave
         bool f0 = false, f1 = false;
-        uint32_t slot = 0;
-        if (mine >= 0 && r != GW_STEP_CONTINUE) {
-            GwRec<MAXH>& rc = recs[mine];
-            const GwSlab s = rc.slab();
-            gw_lane_flush(s, rc.ln);
-            slot = rc.slot;
-            rstate[mine] = GW_RS_FREE;
+        if (have && r != GW_STEP_CONTINUE) {
+            gw_lane_flush(s, ln);
             if (r == GW_STEP_PARKED) {
                 const GwReadCtx* c = s.ctx();
                 f0 = c->pend_n > 0 && c->pend[0].kind == 2;
@@ -362,9 +264,10 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, MINB) gw_flow_kernel(GwSearch
             if (f0) frags[o & MASK] = slot * 2u;
             if (f1) frags[(o + (f0 ? 1u : 0u)) & MASK] = slot * 2u + 1u;
             f_tail += (uint32_t)__popc(b_f0) + (uint32_t)__popc(b_f1);
+            __syncwarp();
         }
-        owned -= (uint32_t)__popc(__ballot_sync(FULL, mine >= 0 && r == GW_STEP_DONE));
-        __syncwarp();
+        owned -= (uint32_t)__popc(__ballot_sync(FULL, have && r == GW_STEP_DONE));
+        if (have && r != GW_STEP_CONTINUE) have = false;
     }
 }
 
@@ -565,29 +468,27 @@ void gwk_scan(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const u
     if (coop) gw_scan_coop_kernel<<<gw_grid(n_tasks * 4, 256), 256, 0, st>>>(ix, slabs, slots, (uint32_t)n_tasks);
     else gw_scan_kernel<<<gw_grid(n_tasks, 128), 128, 0, st>>>(ix, slabs, slots, (uint32_t)n_tasks);
 }
-template <int MAXH, int MINB, int RW>
+template <int MAXH>
 static void gw_flow_attr() {
-    // the search records take most of the shared memory the CTAs of an SM ask for; the rest of the SM's 256 KB is L1 for the work areas
-    const size_t bytes = gw_flow_smem_bytes<MAXH, RW>();
-    cudaFuncSetAttribute(gw_flow_kernel<MAXH, MINB, RW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-    int pct = (int)((bytes + 1024) * MINB * 100 / (228 * 1024)) + 1;
-    cudaFuncSetAttribute(gw_flow_kernel<MAXH, MINB, RW>, cudaFuncAttributePreferredSharedMemoryCarveout, pct > 100 ? 100 : pct);
+    // the lane records take most of the shared memory the two CTAs of an SM ask for; the rest of the SM's 256 KB is L1 for the work areas
+    const size_t bytes = gw_flow_smem_bytes<MAXH>();
+    cudaFuncSetAttribute(gw_flow_kernel<MAXH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    const int pct = (int)((bytes + 1024) * 2 * 100 / (228 * 1024)) + 1;
+    cudaFuncSetAttribute(gw_flow_kernel<MAXH>, cudaFuncAttributePreferredSharedMemoryCarveout, pct > 100 ? 100 : pct);
 }
 void gwk_flow_setup(void) {   // function attributes are per device: called once per aligner (after cudaSetDevice)
-    gw_flow_attr<4, 2, 48>(); gw_flow_attr<4, 2, 40>(); gw_flow_attr<4, 2, 32>(); gw_flow_attr<8, 2, 40>(); gw_flow_attr<GW_MAX_ROWS, 2, 24>();
+    gw_flow_attr<4>(); gw_flow_attr<8>(); gw_flow_attr<GW_MAX_ROWS>();
 }
 void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-              uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh, int records) {
+              uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh) {
     if (!n_active) return;
     GwFlowParams pp;
     pp.cap = fetch < 1 ? 1 : (fetch > 32 ? 32 : fetch);
     pp.batch = batch < 1 ? 1 : batch; pp.age = age < 1 ? 1 : age; pp.flush = flush < 1 ? 1 : flush;
     GwU64x2* h = (GwU64x2*)hist;
-#define GW_FLOW_LAUNCH(H, B, R) gw_flow_kernel<H, B, R><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<H, R>(), st>>>(env, slabs, active, n_active, work_counter, h, pp)
-    if (maxh <= 4) { if (records >= 48) GW_FLOW_LAUNCH(4, 2, 48); else if (records >= 40) GW_FLOW_LAUNCH(4, 2, 40); else GW_FLOW_LAUNCH(4, 2, 32); }
-    else if (maxh <= 8) GW_FLOW_LAUNCH(8, 2, 40);
-    else GW_FLOW_LAUNCH(GW_MAX_ROWS, 2, 24);
-#undef GW_FLOW_LAUNCH
+    if (maxh <= 4) gw_flow_kernel<4><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<4>(), st>>>(env, slabs, active, n_active, work_counter, h, pp);
+    else if (maxh <= 8) gw_flow_kernel<8><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<8>(), st>>>(env, slabs, active, n_active, work_counter, h, pp);
+    else gw_flow_kernel<GW_MAX_ROWS><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<GW_MAX_ROWS>(), st>>>(env, slabs, active, n_active, work_counter, h, pp);
 }
 void gwk_densify(cudaStream_t st, const GwIndexView& ix, int fm, uint32_t step, uint32_t* table, uint32_t n_samples) {
     if (n_samples) gw_densify_kernel<<<gw_grid(n_samples, 256), 256, 0, st>>>(ix, fm, step, table, n_samples);
