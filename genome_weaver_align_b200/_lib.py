@@ -17,7 +17,7 @@ class Config(C.Structure):
     """gw_config_t == AlignmentConfig + AlignmentScoreConfig of the reference"""
     _fields_ = [("k", C.c_float), ("num_split_allowed", C.c_int32), ("match_score", C.c_int32), ("mismatch_penalty", C.c_int32),
                 ("split_open_penalty", C.c_int32), ("indel_end_skip", C.c_int32), ("band_width", C.c_int32), ("report_type", C.c_int32),
-                ("top_l", C.c_int32), ("strategy", C.c_int32)]
+                ("top_l", C.c_int32), ("strategy", C.c_int32), ("extended", C.c_int32)]
 
 
 class Counters(C.Structure):
@@ -65,7 +65,7 @@ SYMBOLS = {
     "gw_locate": (C.c_int, [_P, C.c_int, _P, C.c_uint32, _P]),
     "gw_quick_scan": (C.c_int, [_P, _P, _P, C.c_uint32, C.c_int, C.c_int, _P]),
     "gw_verify_pairs": (C.c_int, [C.c_int, _P, _P, _P, _P, C.c_uint32, C.c_int, _P, _P, C.c_uint32]),
-    "gw_staircase_table": (C.c_int, [C.c_int, C.c_int, _P, C.c_int]),
+    "gw_staircase_table": (C.c_int, [C.c_int, C.c_int, C.c_int, _P, C.c_int]),
     "gw_cyclic_suffix_array": (C.c_int, [_P, C.c_uint64, C.c_int, _P]),
     "gw_max_edit_distance_c": (C.c_int, [C.c_float, C.c_int]),
 }

@@ -23,10 +23,13 @@ class AlignmentConfig:
     """-k -s -M -N -S -P -W -R -L of `genome-weaver align` (same names and defaults as the reference)"""
 
     def __init__(self, k=0.1, numSplitAlowed=1, matchScore=1, mismatchPenalty=3, splitOpenPenalty=11, indelEndSkip=5, bandWidth=31,
-                 reportType="besthit", topL=5):
+                 reportType="besthit", topL=5, extended=False):
         self.k, self.numSplitAlowed, self.matchScore, self.mismatchPenalty = k, numSplitAlowed, matchScore, mismatchPenalty
         self.splitOpenPenalty, self.indelEndSkip, self.bandWidth, self.topL = splitOpenPenalty, indelEndSkip, bandWidth, topL
         self.reportType = reportType
+        # not in the reference: reads on which its StaircaseFilter constructor throws (m >= 156) are aligned with the oracle's `extended`
+        # semantics (out-of-range bit-vector blocks read as 0) instead of coming back READ_REF_ABORT
+        self.extended = extended
 
     def getMaximumEditDistance(self, readLength):
         return L.lib().gw_max_edit_distance_c(C.c_float(self.k), readLength)
@@ -39,6 +42,7 @@ class AlignmentConfig:
         c.split_open_penalty, c.indel_end_skip, c.band_width, c.top_l = self.splitOpenPenalty, self.indelEndSkip, self.bandWidth, self.topL
         rt = self.reportType
         c.report_type = REPORT_TYPES[rt.lower()] if isinstance(rt, str) else int(rt)
+        c.extended = 1 if self.extended else 0
         return c
 
 
@@ -243,11 +247,11 @@ def alignBlockDetailed(pairs, k, device=0):
     return out
 
 
-def staircase_table(m, kk):
+def staircase_table(m, kk, extended=False):
     """StaircaseFilter(m, kk) masks as a (kk+1, ceil(m/64)) uint64 array, and whether the reference constructor throws"""
     nb = (m + 63) // 64
     out = np.zeros((kk + 1) * nb, dtype=np.uint64)
-    rc = L.lib().gw_staircase_table(m, kk, L.ptr(out), len(out))
+    rc = L.lib().gw_staircase_table(m, kk, 1 if extended else 0, L.ptr(out), len(out))
     if rc < 0:
         L.check(rc)
     return out.reshape(kk + 1, nb), rc == 2

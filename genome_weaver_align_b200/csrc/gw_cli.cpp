@@ -40,6 +40,8 @@ struct Batch {
     bool aligned = false;
     std::string sam;            // SAM text of the batch (filled by the format stage of a worker)
     int64_t abort_read = -1;    // first read on which the reference throws (its run stops there), -1: none
+    uint64_t n_unsupported = 0; // reads outside the supported domain (length 0 or > 256, k > 25, work area exhausted)
+    int64_t first_unsupported = -1;
     gw_counters_t counters{};
     void add(const std::string& name, const std::string& seq_, const std::string* qual) {
         names += name; name_off.push_back(names.size());
@@ -215,7 +217,10 @@ int usage() {
             "usage: genome-weaver bwt <fasta> [--device D]\n"
             "       genome-weaver align -r <ref.fa> [-q <query> | <reads.fastq|.fq|.fa|.fasta|.fan>] [-k K] [-s S] [-M n] [-N n] [-S n] [-P n] [-W n]\n"
             "                           [-R besthit|allhits|topL] [-L n] [-m bsf] [--silent] [--gpus N] [--device D] [--batch reads] [--stats]\n"
-            "                           [--keep-going] [--opt name=value]\n");
+            "                           [--keep-going] [--extended] [--opt name=value]\n"
+            "       reads of 1..256 bases with at most 25 differences are aligned; others are written as unmapped records and make the exit\n"
+            "       status 2 unless --keep-going is given; --extended aligns the long reads (156 bases and more) on which the reference's\n"
+            "       suffix filter throws, instead of ending the run there\n");
     return 1;
 }
 
@@ -289,8 +294,12 @@ void worker(int device, const Options* o, Channel<BatchPtr>* in, Channel<BatchPt
             }
             if (rc != GW_OK) fail("align");
             else {
-                for (uint64_t i = 0; i < b->nh; ++i)   // Align.java has no recovery: the first read the reference throws on ends its run
-                    if (b->hits[i].is_head && b->hits[i].status == GW_READ_REF_ABORT) { b->abort_read = b->hits[i].read_index; break; }
+                for (uint64_t i = 0; i < b->nh; ++i) {
+                    if (!b->hits[i].is_head) continue;
+                    if (b->hits[i].status == GW_READ_UNSUPPORTED) { if (!b->n_unsupported++) b->first_unsupported = b->hits[i].read_index; }
+                    // Align.java has no recovery: the first read the reference throws on ends its run
+                    if (b->hits[i].status == GW_READ_REF_ABORT && b->abort_read < 0) b->abort_read = b->hits[i].read_index;
+                }
                 b->aligned = true;
             }
             *busy_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
@@ -358,6 +367,7 @@ int cmd_align(int argc, char** argv) {
         } else if (a == "--silent") o.silent = true;
         else if (a == "--stats") o.stats = true;
         else if (a == "--keep-going") o.keep_going = true;
+        else if (a == "--extended") o.cfg.extended = 1;
         else if (a == "--gpus") { if (!need(&v) || v < 1) return usage(); o.gpus = (int)v; }
         else if (a == "--device") { if (!need(&v)) return usage(); o.device = (int)v; }
         else if (a == "--batch") { if (!need(&v) || v < 1) return usage(); o.batch = (uint32_t)v; }
@@ -397,6 +407,7 @@ int cmd_align(int argc, char** argv) {
     uint64_t n_batches = 0, total_reads = 0;
     gw_counters_t tot{};
     bool aborted = false;
+    uint64_t unsupported = 0;
     std::thread writer([&] {
         std::map<uint64_t, BatchPtr> held;
         uint64_t next = 0;
@@ -414,6 +425,13 @@ int cmd_align(int argc, char** argv) {
                     tot.cutoffs += cur.counters.cutoffs; tot.filtered += cur.counters.filtered;
                     tot.occ_lookups_scan += cur.counters.occ_lookups_scan; tot.occ_lookups_search += cur.counters.occ_lookups_search;
                     tot.occ_lookups_locate += cur.counters.occ_lookups_locate; tot.gpu_launches += cur.counters.gpu_launches;
+                    if (cur.n_unsupported) {
+                        if (!unsupported)
+                            fprintf(stderr, "genome-weaver align: read #%llu (%s) is outside the supported domain (1..256 bases, at most 25 differences); it is written as an unmapped record\n",
+                                    (unsigned long long)(total_reads - cur.n + (uint64_t)cur.first_unsupported),
+                                    cur.names.substr(cur.name_off[(size_t)cur.first_unsupported], cur.name_off[(size_t)cur.first_unsupported + 1] - cur.name_off[(size_t)cur.first_unsupported]).c_str());
+                        unsupported += cur.n_unsupported;
+                    }
                     if (cur.abort_read >= 0 && !o.keep_going) {
                         aborted = true;
                         fprintf(stderr, "genome-weaver align: the reference aborts on read #%llu (%s); output ends there like the reference's (use --keep-going to skip such reads)\n",
@@ -462,6 +480,11 @@ int cmd_align(int argc, char** argv) {
     int rc = 0;
     for (int g = 0; g < G; ++g)
         if (!errs[(size_t)g].empty()) { fprintf(stderr, "genome-weaver align (device %d): %s\n", o.device + g, errs[(size_t)g].c_str()); rc = 1; }
+    if (unsupported) {
+        fprintf(stderr, "genome-weaver align: %llu read(s) outside the supported domain were written as unmapped records%s\n", (unsigned long long)unsupported,
+                o.keep_going ? "" : " (exit status 2; --keep-going accepts them)");
+        if (!o.keep_going && rc == 0) rc = 2;
+    }
     if (o.stats) {
         const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
         double b = 0, op = 0;

@@ -209,10 +209,11 @@ void gw_load_acgt(const std::string& path, std::vector<uint8_t>& codes) {
     std::vector<uint8_t> d = slurp(path);
     if (d.size() < 8) throw GwIoError("truncated " + path);
     const uint64_t n = rd_be64(d.data());
+    if (n >= 0xFFFFFFFFull) throw GwIoError("sequences of 2^32 - 1 symbols or more are not supported: " + path);
     size_t p = 8;
     if (d.size() >= p + 16 && memcmp(d.data() + p, kSnappyMagic, 8) == 0) p += 16;
     std::vector<uint8_t> raw;
-    raw.reserve((size_t)((n + 63) / 64) * 24);
+    raw.reserve((size_t)std::min<uint64_t>(((n + 63) / 64) * 24, (uint64_t)d.size() * 64));
     while (p + 4 <= d.size()) {
         const uint32_t clen = rd_be32(d.data() + p);
         p += 4;
@@ -255,7 +256,9 @@ void gw_load_ssa(const std::string& path, uint64_t* N, int* L, std::vector<uint3
     *N = rd_be64(d.data());
     *L = (int)rd_be32(d.data() + 8);
     const uint64_t cnt = rd_be64(d.data() + 12);
-    if (d.size() < 20 + cnt * 4) throw GwIoError("truncated samples in " + path);
+    if (cnt > (d.size() - 20) / 4) throw GwIoError("truncated samples in " + path);   // (also rejects counts whose byte size would wrap)
+    if (*L <= 0 || cnt != (*N + (uint64_t)*L - 1) / (uint64_t)*L) throw GwIoError("sample count of " + path + " does not match its text size");
+    if (*N >= 0xFFFFFFFFull) throw GwIoError("texts of 2^32 - 1 symbols or more are not supported: " + path);
     samples.resize((size_t)cnt);
     for (uint64_t i = 0; i < cnt; ++i) samples[(size_t)i] = rd_be32(d.data() + 20 + 4 * i);
 }
@@ -334,6 +337,17 @@ void gw_load_index_files(const std::string& fasta_path, GwHostIndex& ix) {
     uint64_t total = 0;
     gw_load_silk(p + ".i.silk", ix.contigs, &total);
     ix.N = total;
+    {   // the contig table must tile [0, N): offsets ascending, every contig inside the text, lengths summing to N
+        uint64_t sum = 0, prev_off = 0;
+        for (size_t i = 0; i < ix.contigs.size(); ++i) {
+            const GwContig& c = ix.contigs[i];
+            if (c.length < 0 || c.offset < 0 || (uint64_t)c.offset + (uint64_t)c.length > total || (i && (uint64_t)c.offset < prev_off))
+                throw GwIoError("contig table of " + p + ".i.silk is inconsistent (contig " + c.name + ")");
+            prev_off = (uint64_t)c.offset;
+            sum += (uint64_t)c.length;
+        }
+        if (ix.contigs.empty() || sum != total) throw GwIoError("contig lengths of " + p + ".i.silk do not sum to the total size");
+    }
     // the five files are independent: read and decode them side by side
     gw_parallel_for(5, 5, [&](uint64_t lo, uint64_t hi, unsigned) {
         for (uint64_t f = lo; f < hi; ++f) {

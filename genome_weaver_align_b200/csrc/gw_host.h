@@ -61,7 +61,8 @@ void gw_load_index_files(const std::string& fasta_path, GwHostIndex& ix);       
 // ---- staircase filter tables (gw_staircase.cpp) ------------------------------------------------------------
 // StaircaseFilter(m, kk) masks (strategy/StaircaseFilter.java:47-73) with Java byte/shift semantics.
 // words: (kk+1) x ceil(m/64). Returns false where the reference constructor throws (ArrayIndexOutOfBoundsException).
-bool gw_staircase_masks(int m, int kk, std::vector<uint64_t>& words);
+// extended: out-of-range block reads give 0 instead of the exception (the oracle's `extended` domain)
+bool gw_staircase_masks(int m, int kk, std::vector<uint64_t>& words, bool extended = false);
 // AlignmentScoreConfig.getMaximumEditDistance (AlignmentScoreConfig.java:40-47)
 int gw_max_edit_distance(float k, int read_length);
 

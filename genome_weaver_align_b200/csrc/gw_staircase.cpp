@@ -5,7 +5,8 @@
 // The masks are a pure function of (m, kk); the Java quirks that change them are kept on purpose:
 //   * chunkStart / chunkLen are `byte`: values above 127 wrap negative;
 //   * `~0L << (size % 64)` with size % 64 == 0 shifts by 0, so _not() zeroes the last block of a 64-multiple length;
-//   * a negative shift length makes _lshift address blocks out of range -> the JVM throws (reported, not emulated).
+//   * a negative shift length makes _lshift address blocks out of range -> the JVM throws (reported, not emulated); in the
+//     `extended` domain such blocks read as 0 instead, as in the oracle's extended mode.
 #include <math.h>
 
 #include "gw_host.h"
@@ -24,10 +25,10 @@ int gw_max_edit_distance(float k, int read_length) {
     return (int)k;
 }
 
-bool gw_staircase_masks(int m, int kk, std::vector<uint64_t>& words) {
+bool gw_staircase_masks(int m, int kk, std::vector<uint64_t>& words, bool extended) {
     const int nb = (m + 63) / 64;
     words.assign((size_t)(kk + 1) * (size_t)nb, 0);
-    if (nb == 0) return false;   // BitVector._not on an empty block array throws
+    if (nb == 0) return extended;   // BitVector._not on an empty block array throws
     const int lastChunk = (m - kk >= 6) ? m * 2 / (kk + 2) : m - kk;
     std::vector<int> chunkStart((size_t)kk + 2, 0);
     const int rest = jbyte(m - lastChunk);
@@ -48,12 +49,12 @@ bool gw_staircase_masks(int m, int kk, std::vector<uint64_t>& words) {
             const int b = i - blockOffset;
             uint64_t high = 0, low = 0;
             if (b >= 0) {
-                if (b >= nb) return false;         // ArrayIndexOutOfBoundsException
-                high = jshl(blk[(size_t)b], offset);
+                if (b >= nb && !extended) return false;         // ArrayIndexOutOfBoundsException (extended: the block reads as 0)
+                high = b >= nb ? 0 : jshl(blk[(size_t)b], offset);
             }
             if (b - 1 >= 0) {
-                if (b - 1 >= nb) return false;
-                low = jushr(blk[(size_t)b - 1] & lowMask, 64 - offset);
+                if (b - 1 >= nb && !extended) return false;
+                low = b - 1 >= nb ? 0 : jushr(blk[(size_t)b - 1] & lowMask, 64 - offset);
             }
             blk[(size_t)i] = high | low;
         }

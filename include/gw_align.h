@@ -52,6 +52,8 @@ typedef struct {
     int32_t report_type;        /* -R : 0 BESTHIT, 1 ALLHITS, 2 TOPL */
     int32_t top_l;              /* -L : 5 */
     int32_t strategy;           /* -m : 0 BSF (only BSF is implemented) */
+    int32_t extended;           /* 0 (default): reads on which the reference's StaircaseFilter constructor throws (m >= 156) come back
+                                   GW_READ_REF_ABORT; 1: such filters are built with out-of-range blocks read as 0 and the read is aligned */
 } gw_config_t;
 
 /* One ReadHit fragment (record/ReadHit.java:42-73). A reported alignment is a chain of 1 or 2 fragments:
@@ -142,7 +144,8 @@ int gw_aligner_set_option(gw_aligner_t*, const char* name, int64_t value);
 /* AlignmentRecord.convert + toSAMLine + SAMOutput.emit (align/record/AlignmentRecord.java:92-276, align/SAMOutput.java:72-82) for the hit
  * records of one batch, on the host. names/quals are concatenated like bases (offset arrays of n_reads+1); quals may be NULL ("*").
  * *out_len in: capacity of out, out: bytes needed/used (GW_E_CAPACITY when too small). lines_per_read (may be NULL) receives the
- * number of SAM lines each read produced (0 where convert returns null or the read is outside the reference's domain). */
+ * number of SAM lines each read produced (0 where convert returns null or the reference throws on the read, GW_READ_REF_ABORT; a read
+ * outside the supported domain, GW_READ_UNSUPPORTED, gets the unmapped "*" record so that the file keeps one entry per read). */
 int gw_sam_format(const gw_index_t*, const char* names, const uint64_t* name_off, const char* bases, const uint64_t* base_off,
                   const char* quals, const uint64_t* qual_off, uint32_t n_reads, const gw_hit_t* hits, uint64_t n_hits,
                   const uint32_t* cigar_ops, char* out, uint64_t* out_len, uint32_t* lines_per_read);
@@ -165,8 +168,9 @@ int gw_quick_scan(const gw_index_t*, const char* bases, const uint64_t* offsets,
  * strings: result[i*4..] = valid, pos, numMismatches, cigar_len ; cigars at cigar_ops[i*cigar_stride..] */
 int gw_verify_pairs(int device, const char* refs, const uint64_t* ref_off, const char* queries, const uint64_t* query_off, uint32_t n,
                     int band_k, int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride);
-/* StaircaseFilter(m, kk) masks (align/strategy/StaircaseFilter.java:47-73): (kk+1) x ceil(m/64) words; returns 2 if the reference throws */
-int gw_staircase_table(int m, int kk, uint64_t* out, int cap_words);
+/* StaircaseFilter(m, kk) masks (align/strategy/StaircaseFilter.java:47-73): (kk+1) x ceil(m/64) words; returns 2 if the reference throws
+ * (never with extended != 0: gw_config_t.extended) */
+int gw_staircase_table(int m, int kk, int extended, uint64_t* out, int cap_words);
 /* CyclicSAIS.SAIS (align/sais/CyclicSAIS.java:223-382): suffix array of the cyclic rotations of an ACGTN string, computed on `device` */
 int gw_cyclic_suffix_array(const char* bases, uint64_t n, int device, uint32_t* sa_out);
 /* AlignmentScoreConfig.getMaximumEditDistance (align/AlignmentScoreConfig.java:40-47) */

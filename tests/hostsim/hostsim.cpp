@@ -66,7 +66,7 @@ uint32_t gwsim_locate(void* h, int which, uint32_t row) {
     return gw_sa_get(((SimIndex*)h)->view, which, row, &steps);
 }
 
-// cfg: k, numSplitAllowed, matchScore, mismatchPenalty, splitOpenPenalty, indelEndSkip, bandWidth, reportType, topL
+// cfg: k, numSplitAllowed, matchScore, mismatchPenalty, splitOpenPenalty, indelEndSkip, bandWidth, reportType, topL, extended
 // returns malloc'ed SAM text; status[n], counters[n*4], lines[n]; *tiers_used = reads that needed a larger work area
 char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bases, const uint64_t* offsets, const char* names,
                   const uint64_t* name_off, const char* quals, const uint64_t* qual_off, uint32_t slab_words, int* status, int* counters,
@@ -93,7 +93,7 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
             base[(size_t)m] = (int32_t)words.size();
             for (int kk = 0; kk <= k + 1; ++kk) {
                 std::vector<uint64_t> w;
-                if (!gw_staircase_masks(m, kk, w)) abortm[(size_t)m] |= 1u << kk;
+                if (!gw_staircase_masks(m, kk, w, cfgv[9] != 0)) abortm[(size_t)m] |= 1u << kk;
                 for (uint64_t x : w) words.push_back((u64)x);
             }
         }

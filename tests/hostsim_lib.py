@@ -12,7 +12,7 @@ _DIR = os.path.join(ROOT, "tests", "hostsim")
 _lib = None
 
 DEFAULT_CFG = dict(k=0.1, num_split_allowed=1, match_score=1, mismatch_penalty=3, split_open_penalty=11,
-                   indel_end_skip=5, band_width=31, report_type=0, top_l=5)
+                   indel_end_skip=5, band_width=31, report_type=0, top_l=5, extended=0)
 
 
 def lib():
@@ -63,8 +63,8 @@ class SimIndex:
     def align(self, names, seqs, quals=None, slab_words=4096, **cfg):
         c = dict(DEFAULT_CFG)
         c.update(cfg)
-        arr = (C.c_double * 9)(c["k"], c["num_split_allowed"], c["match_score"], c["mismatch_penalty"], c["split_open_penalty"],
-                               c["indel_end_skip"], c["band_width"], c["report_type"], c["top_l"])
+        arr = (C.c_double * 10)(c["k"], c["num_split_allowed"], c["match_score"], c["mismatch_penalty"], c["split_open_penalty"],
+                                c["indel_end_skip"], c["band_width"], c["report_type"], c["top_l"], c["extended"])
         n = len(seqs)
         b, boff = concat(seqs)
         nm, noff = concat(names)

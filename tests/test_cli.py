@@ -74,3 +74,45 @@ def test_cli_fasta_reads_and_single_query(tmp_path):
     assert p.returncode == 0, p.stderr
     assert p.stdout == oi.sam_header() + "".join(l + "\n" for l in want["sam"][0])
     oi.close()
+
+
+@pytest.mark.gpu
+def test_cli_reads_outside_the_supported_domain_and_broken_index_files(tmp_path):
+    fa, names, reads, quals = _workload(tmp_path, 50, 3, 51)
+    subprocess.check_call([CLI, "bwt", fa])
+    reads[10] = "ACGT" * 75                          # 300 bases: longer than the 256 the device path takes
+    quals[10] = "I" * 300
+    fq = str(tmp_path / "reads.fastq")
+    with open(fq, "w") as f:
+        for n, r, q in zip(names, reads, quals):
+            f.write("@%s\n%s\n+\n%s\n" % (n, r, q))
+    p = subprocess.run([CLI, "align", "-r", fa, "-k", "3", fq], capture_output=True, text=True)
+    body = [l for l in p.stdout.split("\n") if l and not l.startswith("@")]
+    assert p.returncode == 2 and "outside the supported domain" in p.stderr       # reported, not silently dropped
+    assert len([l for l in body if l.startswith(names[10] + "\t")]) == 1           # the file keeps one record for the read ...
+    assert [l for l in body if l.startswith(names[10] + "\t")][0].split("\t")[1:4] == ["68", "*", "0"]   # ... an unmapped one
+    p = subprocess.run([CLI, "align", "-r", fa, "-k", "3", fq, "--keep-going"], capture_output=True, text=True)
+    assert p.returncode == 0
+    # index files that disagree with their headers are refused when the index is opened (no out-of-bounds reads on the device)
+    import genome_weaver_align_b200 as gw
+    from genome_weaver_align_b200 import _lib as L
+    ssa = fa + ".f.ssa"
+    good = open(ssa, "rb").read()
+    try:
+        for bad in (good[:-8], good[:12] + (2 ** 61).to_bytes(8, "big") + good[20:]):   # two samples short; a count whose size wraps
+            open(ssa, "wb").write(bad)
+            with pytest.raises(L.GwError) as e:
+                gw.FMIndexOnGenome.load(fa, 0)
+            assert e.value.code == L.GW_E_IO
+    finally:
+        open(ssa, "wb").write(good)
+    silk = fa + ".i.silk"
+    text = open(silk).read()
+    try:
+        open(silk, "w").write(text.replace("-length:90000", "-length:95000"))
+        with pytest.raises(L.GwError) as e:
+            gw.FMIndexOnGenome.load(fa, 0)
+        assert e.value.code == L.GW_E_IO
+    finally:
+        open(silk, "w").write(text)
+    gw.FMIndexOnGenome.load(fa, 0).close()

@@ -267,6 +267,14 @@ def test_reference_abort_domain(small):
     assert 2 in want["status"]
 
 
+def test_extended_domain_config4_reads(small):
+    # BASELINE.json configs[3] reads (250 bp, k = 6) in the `extended` domain: no read comes back GW_READ_REF_ABORT, all are aligned
+    # exactly as the oracle's extended mode aligns them
+    reads = synth.simulate_reads(small["g"], 400, 250, 6, 92)
+    batch, want = compare(small["idx"], small["oidx"], reads, gw.AlignmentConfig(k=6, extended=True), dict(k=6, extended=1))
+    assert 2 not in want["status"] and want["status"].count(0) > 300
+
+
 def test_repeats_all_hits_and_topl(tmp_path):
     g = synth.inject_repeats(synth.random_genome(150_000, 4), 5, families=6, min_len=200, max_len=900, copies=(5, 30))
     fa = str(tmp_path / "rep.fa")

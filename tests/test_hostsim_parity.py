@@ -70,6 +70,14 @@ def test_lane_register_copy_is_transparent(rnd, monkeypatch, env):
     _compare(oi, si, synth.simulate_reads(g, 100, 150, 6, 14), k=6)
 
 
+def test_extended_domain(rnd):
+    # config 4 (250 bp, k = 6): in the `extended` domain the reads on which the reference's StaircaseFilter throws are aligned
+    g, oi, si = rnd
+    ro, rs = _compare(oi, si, synth.simulate_reads(g, 80, 250, 6, 9), k=6, extended=1)
+    assert 2 not in ro["status"] and ro["status"].count(0) > 60
+    _compare(oi, si, synth.simulate_reads(g, 60, 200, 3, 10), k=3, extended=1, report_type=1)
+
+
 def test_edge_reads(rnd):
     g, oi, si = rnd
     s = g.tobytes().decode()

@@ -81,6 +81,10 @@ def test_staircase_tables_match_the_oracle():
             assert thrown == (rc == 2), (m, kk)
             if not thrown:
                 assert [int(x) for x in got.reshape(-1)] == list(want), (m, kk)
+            else:   # the `extended` domain: out-of-range blocks read as 0 on both sides
+                got, thrown = aligner.staircase_table(m, kk, extended=True)
+                assert not thrown and O.lib().gwo_staircase_table(m, kk, 1, want, (kk + 1) * nb) == 0
+                assert [int(x) for x in got.reshape(-1)] == list(want), (m, kk)
 
 
 def test_exported_symbols_match_the_header():
