@@ -112,7 +112,7 @@ def simulate_reads(genome, n_reads, length, max_edits, seed, end_skip=5, exact_e
     return reads
 
 
-def simulate_reads_fast(genome, n_reads, length, max_edits, seed, end_skip=5):
+def simulate_reads_fast(genome, n_reads, length, max_edits, seed, end_skip=5, exact_edits=None):
     """vectorised variant for millions of reads: substitutions, single-base insertions and deletions applied with
     numpy gathers (same error model as simulate_reads, different random stream). Returns a (n_reads, length) uint8 array."""
     rng = np.random.default_rng(seed)
@@ -125,6 +125,8 @@ def simulate_reads_fast(genome, n_reads, length, max_edits, seed, end_skip=5):
     sub_mask = np.zeros((n_reads, length), dtype=bool)
     ins_mask = np.zeros((n_reads, length), dtype=bool)
     nedits = rng.integers(0, max_edits + 1, size=n_reads)
+    if exact_edits is not None:
+        nedits = np.full(n_reads, exact_edits)
     for e in range(max_edits):
         active = nedits > e
         pos = rng.integers(end_skip + 1, length - end_skip - 1, size=n_reads)
