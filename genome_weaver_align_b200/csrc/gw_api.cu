@@ -87,9 +87,12 @@ struct gw_index {
     std::vector<GwContig> contigs;
     GwIndexView view;
     DBuf loc[2];   // densified locate table (empty: the .ssa samples serve)
-    DBuf occ[2], ssa[2], ref_lo, ref_hi, ref_nf, ctg_off, ctg_id, ctg_rank;
+    DBuf occ_all;  // both occurrence tables in ONE allocation, so that one L2 access-policy window can cover them
+    size_t occ_bytes = 0;
+    DBuf ssa[2], ref_lo, ref_hi, ref_nf, ctg_off, ctg_id, ctg_rank;
     ~gw_index() {
-        for (int s = 0; s < 2; ++s) { occ[s].release(); ssa[s].release(); loc[s].release(); }
+        occ_all.release();
+        for (int s = 0; s < 2; ++s) { ssa[s].release(); loc[s].release(); }
         ref_lo.release(); ref_hi.release(); ref_nf.release(); ctg_off.release(); ctg_id.release(); ctg_rank.release();
     }
 };
@@ -111,9 +114,13 @@ void make_device_index(gw_index* ix, const GwHostIndex& h, int device) {
     gw_layout_index(h, img);
     GwIndexView& v = ix->view;
     v = img.view;
+    const size_t occ0 = (img.occ[0].size() * sizeof(GwOccBlock) + 255) & ~(size_t)255, occ1 = img.occ[1].size() * sizeof(GwOccBlock);
+    ix->occ_all.ensure(std::max<size_t>(occ0 + occ1, 16));
+    ix->occ_bytes = occ0 + occ1;
     for (int s = 0; s < 2; ++s) {
-        upload(ix->occ[s], img.occ[s].data(), img.occ[s].size() * sizeof(GwOccBlock));
-        v.occ[s] = ix->occ[s].as<GwOccBlock>();
+        GwOccBlock* dst = reinterpret_cast<GwOccBlock*>(ix->occ_all.as<char>() + (s ? occ0 : 0));
+        if (!img.occ[s].empty()) CK(cudaMemcpy(dst, img.occ[s].data(), img.occ[s].size() * sizeof(GwOccBlock), cudaMemcpyHostToDevice));
+        v.occ[s] = dst;
         upload(ix->ssa[s], h.ssa[s].data(), h.ssa[s].size() * sizeof(uint32_t));
         v.ssa[s] = ix->ssa[s].as<uint32_t>();
         v.loc[s] = v.ssa[s];

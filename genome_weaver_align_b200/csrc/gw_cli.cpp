@@ -24,6 +24,8 @@
 #include <thread>
 #include <vector>
 
+#include <zlib.h>
+
 #include "../../include/gw_align.h"
 
 namespace {
@@ -58,48 +60,23 @@ bool ends_with(const std::string& s, const char* suf) {
     return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
 }
 
-class LineReader {   // buffered line reader over a 16 MB window; lines are handed out as views into the window
+// lines of a block of text held in memory; views are valid as long as the block is
+class LineReader {
   public:
-    explicit LineReader(FILE* f) : f_(f), buf_(16u << 20) {}
-    // next line without its terminator; the view is valid until the next call
+    LineReader(const char* p, size_t n) : p_(p), end_(p + n) {}
+    // next line without its terminator
     bool next(const char*& p, size_t& n) {
-        for (;;) {
-            const char* s = buf_.data() + pos_;
-            const char* e = (const char*)memchr(s, '\n', len_ - pos_);
-            if (e) {
-                p = s; n = (size_t)(e - s);
-                pos_ += n + 1;
-                if (n && p[n - 1] == '\r') --n;
-                return true;
-            }
-            if (eof_) {
-                if (pos_ == len_) return false;
-                p = s; n = len_ - pos_;
-                pos_ = len_;
-                if (n && p[n - 1] == '\r') --n;
-                return true;
-            }
-            // refill: keep the unfinished line at the front of the window (grow it for lines longer than the window)
-            const size_t rest = len_ - pos_;
-            if (rest) memmove(buf_.data(), buf_.data() + pos_, rest);
-            if (rest == buf_.size()) buf_.resize(buf_.size() * 2);
-            pos_ = 0; len_ = rest;
-            const size_t got = fread(buf_.data() + len_, 1, buf_.size() - len_, f_);
-            len_ += got;
-            if (got == 0) eof_ = true;
-        }
-    }
-    bool next(std::string& line) {
-        const char* p; size_t n;
-        if (!next(p, n)) { line.clear(); return false; }
-        line.assign(p, n);
+        if (p_ >= end_) return false;
+        const char* e = (const char*)memchr(p_, '\n', (size_t)(end_ - p_));
+        p = p_;
+        n = (size_t)((e ? e : end_) - p_);
+        p_ = e ? e + 1 : end_;
+        if (n && p[n - 1] == '\r') --n;
         return true;
     }
   private:
-    FILE* f_;
-    std::vector<char> buf_;
-    size_t pos_ = 0, len_ = 0;
-    bool eof_ = false;
+    const char* p_;
+    const char* end_;
 };
 
 std::string trim(const std::string& s) {
@@ -110,14 +87,13 @@ std::string trim(const std::string& s) {
 }
 
 // FASTQ: 4 lines per record; read name = header line minus '@' (lens FASTQ.scala:35-52). Lines go straight from the
-// reader's window into the batch arrays.
-struct FastqSource {
-    LineReader lr;
-    explicit FastqSource(FILE* f) : lr(f) {}
-    bool next(Batch& b) {
-        const char* p; size_t n;
+// block into the batch arrays.
+void parse_fastq(const char* data, size_t len, Batch& b) {
+    LineReader lr(data, len);
+    const char* p; size_t n;
+    for (;;) {
         for (;;) {
-            if (!lr.next(p, n)) return false;
+            if (!lr.next(p, n)) return;
             if (n) break;
         }
         const size_t n0 = b.names.size(), b0 = b.bases.size();
@@ -130,40 +106,190 @@ struct FastqSource {
             b.bases.append(p, n);
             ok = lr.next(p, n) && lr.next(p, n);
         }
-        if (!ok) { b.names.resize(n0); b.bases.resize(b0); return false; }   // truncated record: stop like FastqReader does at EOF
+        if (!ok) { b.names.resize(n0); b.bases.resize(b0); return; }   // truncated record: stop like FastqReader does at EOF
         b.quals.append(p, n);
         b.name_off.push_back(b.names.size()); b.base_off.push_back(b.bases.size()); b.qual_off.push_back(b.quals.size());
         ++b.n;
-        return true;
     }
-};
+}
 
 // FASTA reads: name = first whitespace-delimited token of the description line, sequence lines concatenated, no quality
-struct FastaSource {
-    LineReader lr;
-    std::string line, pending_name, seq;
-    bool have = false, eof = false;
-    explicit FastaSource(FILE* f) : lr(f) {}
-    static std::string pick_name(const std::string& desc) {
+void parse_fasta(const char* data, size_t len, Batch& b) {
+    LineReader lr(data, len);
+    const char* p; size_t n;
+    bool have = false;
+    std::string name, seq;
+    auto pick_name = [](const char* q, size_t m) {
         size_t a = 0;
-        while (a < desc.size() && (unsigned char)desc[a] <= ' ') ++a;
-        size_t b = a;
-        while (b < desc.size() && (unsigned char)desc[b] > ' ') ++b;
-        return desc.substr(a, b - a);
+        while (a < m && (unsigned char)q[a] <= ' ') ++a;
+        size_t e = a;
+        while (e < m && (unsigned char)q[e] > ' ') ++e;
+        return std::string(q + a, e - a);
+    };
+    while (lr.next(p, n)) {
+        if (n && p[0] == '>') {
+            if (have) b.add(name, seq, nullptr);
+            have = true; name = pick_name(p + 1, n - 1); seq.clear();
+        } else if (have)
+            seq += trim(std::string(p, n));
     }
-    bool next(Batch& b) {
-        while (!eof) {
-            if (!lr.next(line)) { eof = true; break; }
-            if (!line.empty() && line[0] == '>') {
-                const std::string nm = pick_name(line.substr(1));
-                if (have) { b.add(pending_name, seq, nullptr); pending_name = nm; seq.clear(); return true; }
-                have = true; pending_name = nm; seq.clear();
-            } else if (have)
-                seq += trim(line);
+    if (have) b.add(name, seq, nullptr);
+}
+
+// ---- byte sources (ReadReaderFactory.createReader :126-153: plain, .gz through GZIPInputStream, .snap through SnappyInputStream) --
+struct ByteSource {
+    virtual ~ByteSource() {}
+    virtual size_t read(char* dst, size_t cap) = 0;   // 0: end of the stream
+    virtual const char* error() const { return nullptr; }
+};
+struct PlainSource : ByteSource {
+    FILE* f;
+    explicit PlainSource(FILE* f_) : f(f_) {}
+    ~PlainSource() override { if (f) fclose(f); }
+    size_t read(char* dst, size_t cap) override { return fread(dst, 1, cap, f); }
+};
+struct GzSource : ByteSource {
+    gzFile g;
+    std::string err;
+    explicit GzSource(gzFile g_) : g(g_) { gzbuffer(g, 1u << 20); }
+    ~GzSource() override { if (g) gzclose(g); }
+    size_t read(char* dst, size_t cap) override {
+        const int n = gzread(g, dst, (unsigned)std::min<size_t>(cap, 1u << 30));
+        if (n < 0) { int e = 0; err = gzerror(g, &e); return 0; }
+        return (size_t)n;
+    }
+    const char* error() const override { return err.empty() ? nullptr : err.c_str(); }
+};
+// snappy-java stream (SnappyOutputStream): 8-byte magic 82 'S' 'N' 'A' 'P' 'P' 'Y' 00, BE int version, BE int compatible version, then
+// chunks [BE int32 compressed length][raw Snappy block]
+struct SnapSource : ByteSource {
+    FILE* f;
+    std::string err;
+    std::vector<char> out;
+    size_t pos = 0;
+    bool started = false;
+    explicit SnapSource(FILE* f_) : f(f_) {}
+    ~SnapSource() override { if (f) fclose(f); }
+    static bool uncompress(const unsigned char* in, size_t n, std::vector<char>& o) {   // raw Snappy block format
+        size_t p = 0, ulen = 0;
+        int shift = 0;
+        for (;;) {
+            if (p >= n || shift > 35) return false;
+            const unsigned char c = in[p++];
+            ulen |= (size_t)(c & 0x7F) << shift;
+            if (!(c & 0x80)) break;
+            shift += 7;
         }
-        if (have) { b.add(pending_name, seq, nullptr); have = false; return true; }
-        return false;
+        o.clear();
+        o.reserve(ulen);
+        while (p < n) {
+            const unsigned char tag = in[p++];
+            size_t len, off;
+            if ((tag & 3) == 0) {   // literal
+                len = (size_t)(tag >> 2) + 1;
+                if (len > 60) {
+                    const size_t nb = len - 60;
+                    if (p + nb > n) return false;
+                    len = 0;
+                    for (size_t i = 0; i < nb; ++i) len |= (size_t)in[p + i] << (8 * i);
+                    len += 1; p += nb;
+                }
+                if (p + len > n) return false;
+                o.insert(o.end(), (const char*)in + p, (const char*)in + p + len);
+                p += len;
+                continue;
+            }
+            if ((tag & 3) == 1) { if (p + 1 > n) return false; len = (size_t)((tag >> 2) & 7) + 4; off = ((size_t)(tag >> 5) << 8) | in[p]; p += 1; }
+            else if ((tag & 3) == 2) { if (p + 2 > n) return false; len = (size_t)(tag >> 2) + 1; off = (size_t)in[p] | ((size_t)in[p + 1] << 8); p += 2; }
+            else { if (p + 4 > n) return false; len = (size_t)(tag >> 2) + 1; off = (size_t)in[p] | ((size_t)in[p + 1] << 8) | ((size_t)in[p + 2] << 16) | ((size_t)in[p + 3] << 24); p += 4; }
+            if (off == 0 || off > o.size()) return false;
+            const size_t from = o.size() - off;
+            for (size_t i = 0; i < len; ++i) o.push_back(o[from + i]);   // may overlap its own output
+        }
+        return o.size() == ulen;
     }
+    bool next_chunk() {
+        unsigned char h[16];
+        if (!started) {
+            started = true;
+            static const unsigned char magic[8] = {0x82, 'S', 'N', 'A', 'P', 'P', 'Y', 0};
+            if (fread(h, 1, 16, f) != 16 || memcmp(h, magic, 8) != 0) { err = "not a snappy-java stream"; return false; }
+        }
+        if (fread(h, 1, 4, f) != 4) return false;   // end of the stream
+        const size_t clen = ((size_t)h[0] << 24) | ((size_t)h[1] << 16) | ((size_t)h[2] << 8) | (size_t)h[3];
+        std::vector<unsigned char> c(clen);
+        if (fread(c.data(), 1, clen, f) != clen || !uncompress(c.data(), clen, out)) { err = "corrupt snappy chunk"; return false; }
+        pos = 0;
+        return true;
+    }
+    size_t read(char* dst, size_t cap) override {
+        while (pos >= out.size()) if (!next_chunk()) return 0;
+        const size_t n = std::min(cap, out.size() - pos);
+        memcpy(dst, out.data() + pos, n);
+        pos += n;
+        return n;
+    }
+    const char* error() const override { return err.empty() ? nullptr : err.c_str(); }
+};
+
+// a block of the read file that holds whole records: parsed into one batch by one of the parser threads
+struct Chunk {
+    uint64_t seq = 0;
+    std::vector<char> data;
+};
+
+// Cuts the byte stream into chunks of whole records — at most `max_reads` records and about `target` bytes each — so that several
+// threads can parse them side by side; the batches keep the order of the file through their sequence numbers.
+class RecordSplitter {
+  public:
+    RecordSplitter(ByteSource* src, bool fasta, uint32_t max_reads, size_t target) : src_(src), fasta_(fasta), max_reads_(max_reads), target_(target) {}
+    bool next(std::vector<char>& out) {
+        for (;;) {
+            // scan what is buffered: `cut_` is the end of the last whole record seen, `recs_` how many records end there
+            while (scan_ < buf_.size()) {
+                const char* base = buf_.data();
+                const char* e = (const char*)memchr(base + scan_, '\n', buf_.size() - scan_);
+                if (!e) break;
+                const size_t ls = scan_, le = (size_t)(e - base);   // the line is [ls, le)
+                scan_ = le + 1;
+                if (fasta_) {
+                    if (le > ls && base[ls] == '>') { if (seen_header_) { ++recs_; cut_ = ls; } seen_header_ = true; }
+                } else {
+                    const bool blank = le == ls || (le == ls + 1 && base[ls] == '\r');
+                    if (line_in_rec_ == 0 && blank) { cut_ = scan_; continue; }   // blank lines between records belong to nobody
+                    if (++line_in_rec_ == 4) { line_in_rec_ = 0; ++recs_; cut_ = scan_; }
+                }
+                if (recs_ >= max_reads_ || (cut_ >= target_ && recs_ > 0)) return emit(out, cut_);
+            }
+            if (eof_) {
+                if (buf_.empty()) return false;
+                return emit(out, buf_.size());   // the tail (a FASTA record ends at the end of the file; a cut FASTQ record is dropped by the parser)
+            }
+            const size_t old = buf_.size();
+            buf_.resize(old + (8u << 20));
+            const size_t got = src_->read(buf_.data() + old, 8u << 20);
+            buf_.resize(old + got);
+            if (got == 0) eof_ = true;
+        }
+    }
+  private:
+    bool emit(std::vector<char>& out, size_t upto) {
+        out.assign(buf_.begin(), buf_.begin() + (long)upto);
+        buf_.erase(buf_.begin(), buf_.begin() + (long)upto);
+        scan_ -= std::min(scan_, upto);
+        cut_ = 0; recs_ = 0;
+        if (fasta_) seen_header_ = scan_ > 0 ? seen_header_ : false;
+        return true;
+    }
+    ByteSource* src_;
+    bool fasta_;
+    uint32_t max_reads_;
+    size_t target_;
+    std::vector<char> buf_;
+    size_t scan_ = 0, cut_ = 0;
+    uint32_t recs_ = 0;
+    int line_in_rec_ = 0;
+    bool seen_header_ = false, eof_ = false;
 };
 
 // ---- bounded queues between the pipeline stages ---------------------------------------------------------------------
@@ -215,7 +341,7 @@ struct Options {
 int usage() {
     fprintf(stderr,
             "usage: genome-weaver bwt <fasta> [--device D]\n"
-            "       genome-weaver align -r <ref.fa> [-q <query> | <reads.fastq|.fq|.fa|.fasta|.fan>] [-k K] [-s S] [-M n] [-N n] [-S n] [-P n] [-W n]\n"
+            "       genome-weaver align -r <ref.fa> [-q <query> | <reads.fastq|.fq|.fa|.fasta|.fan[.gz|.snap]>] [-k K] [-s S] [-M n] [-N n] [-S n] [-P n] [-W n]\n"
             "                           [-R besthit|allhits|topL] [-L n] [-m bsf] [--silent] [--gpus N] [--device D] [--batch reads] [--stats]\n"
             "                           [--keep-going] [--extended] [--opt name=value]\n"
             "       reads of 1..256 bases with at most 25 differences are aligned; others are written as unmapped records and make the exit\n"
@@ -382,16 +508,27 @@ int cmd_align(int argc, char** argv) {
     if (o.ref.empty()) { fprintf(stderr, "no reference (-r) is given\n"); return 1; }
     if (o.query.empty() && o.files.empty()) { fprintf(stderr, "no query is given\n"); return 1; }   // Align.java:79-80
 
-    // open the read source before any device work (ReadReaderFactory.createReader: unsupported types fail up front)
-    FILE* f = nullptr;
+    // open the read source before any device work (ReadReaderFactory.createReader :126-153: unsupported types fail up front;
+    // ".gz" / ".snap" wrap the stream, the extension underneath picks the record format)
+    std::unique_ptr<ByteSource> src;
     bool fasta_reads = false;
     if (o.query.empty()) {
         const std::string& p = o.files[0];
-        if (ends_with(p, ".gz") || ends_with(p, ".snap")) { fprintf(stderr, "compressed read files are not supported: %s\n", p.c_str()); return 1; }
-        if (ends_with(p, ".fa") || ends_with(p, ".fasta") || ends_with(p, ".fan")) fasta_reads = true;
-        else if (!(ends_with(p, ".fastq") || ends_with(p, ".fq"))) { fprintf(stderr, "Unsupported file type: %s\n", p.c_str()); return 1; }
-        f = fopen(p.c_str(), "rb");
-        if (!f) { fprintf(stderr, "cannot open %s\n", p.c_str()); return 1; }
+        std::string prefix = p;
+        const bool gz = ends_with(p, ".gz"), snap = ends_with(p, ".snap");
+        if (gz) prefix = p.substr(0, p.size() - 3);
+        if (snap) prefix = p.substr(0, p.size() - 5);
+        if (ends_with(prefix, ".fa") || ends_with(prefix, ".fasta") || ends_with(prefix, ".fan")) fasta_reads = true;
+        else if (!(ends_with(prefix, ".fastq") || ends_with(prefix, ".fq"))) { fprintf(stderr, "Unsupported file type: %s\n", p.c_str()); return 1; }
+        if (gz) {
+            gzFile g = gzopen(p.c_str(), "rb");
+            if (!g) { fprintf(stderr, "cannot open %s\n", p.c_str()); return 1; }
+            src.reset(new GzSource(g));
+        } else {
+            FILE* f = fopen(p.c_str(), "rb");
+            if (!f) { fprintf(stderr, "cannot open %s\n", p.c_str()); return 1; }
+            if (snap) src.reset(new SnapSource(f)); else src.reset(new PlainSource(f));
+        }
     }
 
     const auto t_start = std::chrono::steady_clock::now();
@@ -452,32 +589,47 @@ int cmd_align(int argc, char** argv) {
         tok->seq = n_batches++;
         to_gpu.push(std::move(tok));
     }
+    std::string read_err;
     if (!o.query.empty()) {   // ReadReaderFactory.singleQueryReader :165-190: one read named "read", no quality
         BatchPtr b(new Batch());
         b->seq = n_batches++;
         b->add("read", o.query, nullptr);
         to_gpu.push(std::move(b));
     } else {
-        FastqSource fq(f);
-        FastaSource fa(f);
+        // this thread cuts the stream into chunks of whole records; the parser threads turn chunks into batches side by side (a batch
+        // carries the sequence number of its chunk, the writer puts the SAM text back in that order)
+        const unsigned P = std::max(2u, std::min(8u, std::thread::hardware_concurrency() / 4u));
+        Channel<std::unique_ptr<Chunk>> chunks(P * 2);
+        std::vector<std::thread> parsers;
+        for (unsigned t = 0; t < P; ++t)
+            parsers.emplace_back([&] {
+                std::unique_ptr<Chunk> c;
+                while (chunks.pop(c)) {
+                    BatchPtr b(new Batch());
+                    b->seq = c->seq;
+                    b->bases.reserve(c->data.size() / 2);
+                    if (fasta_reads) parse_fasta(c->data.data(), c->data.size(), *b); else parse_fastq(c->data.data(), c->data.size(), *b);
+                    c.reset();
+                    to_gpu.push(std::move(b));   // (an empty batch still travels: the writer waits for every sequence number)
+                }
+            });
+        RecordSplitter split(src.get(), fasta_reads, o.batch, (size_t)64 << 20);
         for (;;) {
-            BatchPtr b(new Batch());
-            b->seq = n_batches;
-            b->bases.reserve((size_t)o.batch * 104);
-            while (b->n < o.batch && (fasta_reads ? fa.next(*b) : fq.next(*b))) {}
-            if (!b->n) break;
-            ++n_batches;
-            const bool last = b->n < o.batch;
-            to_gpu.push(std::move(b));
-            if (last) break;
+            std::unique_ptr<Chunk> c(new Chunk());
+            if (!split.next(c->data)) break;
+            c->seq = n_batches++;
+            chunks.push(std::move(c));
         }
-        fclose(f);
+        if (src->error()) read_err = src->error();
+        chunks.close();
+        for (auto& t : parsers) t.join();
     }
     to_gpu.close();
     for (auto& w : workers) w.join();
     done.close();
     writer.join();
     int rc = 0;
+    if (!read_err.empty()) { fprintf(stderr, "genome-weaver align: %s: %s\n", o.files[0].c_str(), read_err.c_str()); rc = 1; }
     for (int g = 0; g < G; ++g)
         if (!errs[(size_t)g].empty()) { fprintf(stderr, "genome-weaver align (device %d): %s\n", o.device + g, errs[(size_t)g].c_str()); rc = 1; }
     if (unsupported) {

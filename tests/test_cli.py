@@ -52,7 +52,39 @@ def test_cli_fastq_whole_sam(tmp_path):
         assert '"reads": 3000' in p.stderr
     p = subprocess.run([CLI, "align", "-r", fa, "-k", "3", fq, "--silent"], capture_output=True, text=True)
     assert p.returncode == 0 and p.stdout == ""      # AlignmentConfig.java:49-50
+    # compressed read files (ReadReaderFactory.java:128-140): gzip, and the snappy-java stream of ".snap"
+    import gzip
+    raw = open(fq, "rb").read()
+    with gzip.open(fq + ".gz", "wb") as f:
+        f.write(raw)
+    with open(fq + ".snap", "wb") as f:
+        f.write(_snappy_java_stream(raw))
+    for path in (fq + ".gz", fq + ".snap"):
+        p = subprocess.run([CLI, "align", "-r", fa, "-k", "3", path, "--batch", "900"], capture_output=True, text=True)
+        assert p.returncode == 0, p.stderr
+        assert p.stdout == expect, path
     oi.close()
+
+
+def _snappy_java_stream(data, chunk=32 * 1024):
+    """SnappyOutputStream framing (magic, version 1, compatible version 1, then [BE int32 length][raw Snappy block] per 32 KiB chunk) with
+    literal-only Snappy blocks: valid input for any Snappy decoder"""
+    out = bytearray(b"\x82SNAPPY\x00" + (1).to_bytes(4, "big") + (1).to_bytes(4, "big"))
+    for p in range(0, len(data), chunk):
+        piece = data[p:p + chunk]
+        blk = bytearray()
+        n = len(piece)
+        while True:   # uncompressed length as a varint
+            blk.append((n & 0x7F) | (0x80 if n > 0x7F else 0))
+            n >>= 7
+            if not n:
+                break
+        for q in range(0, len(piece), 60):   # literals of at most 60 bytes: one-byte tags
+            lit = piece[q:q + 60]
+            blk.append((len(lit) - 1) << 2)
+            blk += lit
+        out += len(blk).to_bytes(4, "big") + blk
+    return bytes(out)
 
 
 @pytest.mark.gpu
