@@ -120,3 +120,32 @@ def test_verifier_body_against_oracle():
         assert (a is None) == (b is None)
         if a:
             assert (a["cigar"], a["pos"], a["nm"]) == (b["cigar"], b["pos"], b["nm"]), (ref, q)
+
+
+def test_verifier_many_differences_and_unrelated_windows():
+    # alignments that leave the band staged for the traceback (more than 15 differences), unrelated windows, windows shorter than the
+    # query: the recomputing verifier must still give what alignBlockDetailed gives
+    import random
+    rnd_ = random.Random(11)
+    for t in range(400):
+        m = rnd_.choice([5, 30, 63, 64, 65, 100, 127, 128, 129, 150, 200, 250, 256])
+        q = "".join(rnd_.choice("ACGT") for _ in range(m))
+        kind = t % 4
+        if kind == 0:   # unrelated window
+            ref = "".join(rnd_.choice("ACGT") for _ in range(rnd_.randint(1, m + 20)))
+        else:
+            ref = list("".join(rnd_.choice("ACGT") for _ in range(rnd_.randint(0, 12))) + q + "".join(rnd_.choice("ACGT") for _ in range(rnd_.randint(0, 12))))
+            for _e in range(rnd_.randint(0, 45 if kind == 1 else 12)):
+                p_ = rnd_.randrange(len(ref))
+                r = rnd_.random()
+                if r < 0.4:
+                    ref[p_] = rnd_.choice("ACGTN")
+                elif r < 0.7:
+                    ref.insert(p_, rnd_.choice("ACGT"))
+                elif len(ref) > 1:
+                    del ref[p_]
+            ref = "".join(ref)
+        a, b = O.align_block_detailed(ref, q, 31), H.verify_pair(ref, q, 31)
+        assert (a is None) == (b is None), (ref, q)
+        if a:
+            assert (a["cigar"], a["pos"], a["nm"]) == (b["cigar"], b["pos"], b["nm"]), (ref, q)
