@@ -50,6 +50,15 @@ CONFIGS = {
 REPORT = {"besthit": 0, "allhits": 1, "topl": 2}
 
 
+_T0 = time.time()
+
+
+def log(msg):
+    """stage log on stderr (the big configs spend minutes in set-up: a run that is cut short must say where it was)"""
+    sys.stderr.write("[bench %7.1fs] %s\n" % (time.time() - _T0, msg))
+    sys.stderr.flush()
+
+
 def spec_of(args):
     s = dict(CONFIGS[args.config])
     if args.genome_bp:
@@ -305,18 +314,24 @@ def run_ours(args):
             dist.barrier()
 
     spec = spec_of(args)
+    log("config %d: drawing the genome" % args.config)
     contigs, genome = make_genome(args, spec)
     t_build, how = 0.0, "cached"
     if rank == 0:
+        log("genome ready; FASTA + index files")
         fa, t_build, how = ensure_index(args, spec, contigs, use_gpu=True, device=local)
+        log("index files ready (%s, %.1f s)" % (how, t_build))
     barrier()
     fa = os.path.join(cache_dir(args, spec), "genome.fa")
     t_open = time.time()
     idx = gw.FMIndexOnGenome.load(fa, local)
     t_open = time.time() - t_open
+    log("index open on the device in %.1f s (locate table step %d)" % (t_open, idx.locateStep()))
     if args.locate_step is not None:
         idx.locateTable(args.locate_step)
+        log("locate table step %d" % idx.locateStep())
     groups = make_reads(spec, genome, rank)
+    log("reads drawn")
     index_gb = (genome.size / 128 * 64 * 2 + genome.size / 8 + genome.size * 3 / 8 + (genome.size * 8 / idx.locateStep() if idx.locateStep() < 32 else 0)) / 1e9
     del genome, contigs
     bases, offsets, m_max = flatten(groups)
@@ -350,6 +365,7 @@ def run_ours(args):
         d_cig = torch.empty(cig_cap, dtype=torch.int32, device=dev)
         rc = step_device()
     L.check(rc)
+    log("first device-resident batch done")
     for _ in range(max(0, args.warmup - 1)):
         L.check(step_device())
     fam = np.zeros(6)
@@ -384,6 +400,7 @@ def run_ours(args):
         L.check(lib.gw_align_batch(bsf._h, h_bases.data_ptr(), h_off.data_ptr(), n, h_hits.data_ptr(), C.byref(a), h_cig.data_ptr(), C.byref(b), None))
         return a.value, b.value
 
+    log("device-resident arm timed: %.1f ms per step" % (1000.0 * dev_time / args.steps))
     for _ in range(min(args.warmup, 1)):
         step_host()
     barrier()
@@ -464,10 +481,13 @@ def run_ours(args):
             pick = sample_indices(n, n_s)
             seqs = [bases[int(offsets[i]):int(offsets[i + 1])].tobytes().decode() for i in pick]
             import oracle_lib as O
+            log("end-to-end arm timed; opening the oracle's index")
             t_oo = time.time()
             oi = O.OracleIndex.load(fa)
             t_oo = time.time() - t_oo
+            log("oracle index open in %.1f s; aligning %d sample reads on %d threads" % (t_oo, len(seqs), threads))
             v, res = oracle_run(fa, seqs, threads, spec, oi)
+            log("oracle sample done")
             if world == 1:
                 v1, _ = oracle_run(fa, seqs[: max(1, len(seqs) // max(threads, 1))], 1, spec, oi)
                 line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",

@@ -149,12 +149,17 @@ void densify_index(gw_index* ix, int step) {
     for (int s = 0; s < 2; ++s) { v.loc[s] = v.ssa[s]; ix->loc[s].release(); }
     v.loc_step = GW_SSA_L;
     if (step >= GW_SSA_L || ix->N == 0) return;
+    DBuf ctr;
+    ctr.ensure(16);
     for (int s = 0; s < 2; ++s) {
         const size_t entries = (size_t)((ix->N + step - 1) / step);
         ix->loc[s].ensure(entries * 4);
         CK(cudaMemset(ix->loc[s].p, 0xFF, entries * 4));
-        gwk_densify(0, v, s, (uint32_t)step, ix->loc[s].as<uint32_t>(), v.n_ssa);
+        CK(cudaMemset(ctr.p, 0, 16));
+        gwk_densify(0, v, s, (uint32_t)step, ix->loc[s].as<uint32_t>(), v.n_ssa, ctr.as<uint32_t>());
+        CK(cudaDeviceSynchronize());
     }
+    ctr.release();
     CK(cudaDeviceSynchronize());
     CK(cudaGetLastError());
     for (int s = 0; s < 2; ++s) v.loc[s] = ix->loc[s].as<uint32_t>();

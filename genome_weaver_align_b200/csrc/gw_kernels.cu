@@ -14,6 +14,8 @@
 #include "gw_kernels.h"
 #include <stdlib.h>
 
+#include <algorithm>
+
 
 // ---------------------------------------------------------------------------------------------------------
 __global__ void gw_prep_kernel(GwBatchView bv, u64* const* slabs, const uint32_t* slots, uint32_t n, uint32_t read_base, GwSlabParams sp) {
@@ -273,21 +275,42 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, 2) gw_flow_kernel(GwSearchEnv
 
 // Densifies the locate table of one index. The LF walk that starts at a sampled row (a multiple of GW_SSA_L) passes through every row
 // whose own walk ends at the NEXT sampled row it reaches — the rows SparseSuffixArray.get resolves with that sample
-// (SparseSuffixArray.java:141-161). One thread per sampled row walks twice: once to find that next sample and the distance to it,
-// once to store, for every row of the walk that is a multiple of `step`, the value the reference computes there:
-// (sample + remaining steps + N) % N. The walks of all threads together visit every row once (LF is a permutation).
-__global__ void __launch_bounds__(256) gw_densify_kernel(GwIndexView ix, int fm, uint32_t step, uint32_t* table, uint32_t n_samples) {
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n_samples) return;
-    const uint32_t start = t * GW_SSA_L;
-    table[start / step] = gw_ld32(ix.ssa[fm] + t);
-    uint32_t cursor = gw_suffix_link(ix, fm, start), len = 1;
-    while ((cursor % GW_SSA_L) != 0) { cursor = gw_suffix_link(ix, fm, cursor); ++len; }
-    const uint32_t smp = gw_ld32(ix.ssa[fm] + cursor / GW_SSA_L);
-    cursor = gw_suffix_link(ix, fm, start);
-    for (uint32_t i = 1; i < len; ++i) {   // row `cursor` reaches the sample after len - i steps
-        if ((cursor & (step - 1u)) == 0) table[cursor / step] = (uint32_t)(((u64)smp + (u64)(len - i) + ix.N) % ix.N);
+// (SparseSuffixArray.java:141-161): a row i steps into the walk, len - i steps before its end, gets (sample_end + len - i) % N. Since
+// one LF step moves one position back in the text that is sample_start - i, and the walk checks it when it arrives: sample_start ==
+// (sample_end + len) % N. (It always holds for the suffix array of a primitive text; should it not, the walk is done a second time
+// with the reference's own formula.) The walks have geometric lengths, so the lanes do not own one walk each: every lane takes the
+// next sampled rows from a shared counter as soon as its walk ends, and the warp's loop body is ONE LF step for all of its lanes.
+__global__ void __launch_bounds__(256) gw_densify_kernel(GwIndexView ix, int fm, uint32_t step, uint32_t* table, uint32_t n_samples, uint32_t* counter) {
+    const uint32_t CHUNK = 8;
+    const u64 N = ix.N;
+    uint32_t next = 0, chunk_end = 0;
+    uint32_t cursor = 0, start = 0, len = 0, redo_len = 0, redo_smp = 0;
+    u64 pos = 0;
+    int mode = 0;   // 0: no walk, 1: walking, 2: walking again with the end sample known
+    for (;;) {
+        if (mode == 0) {
+            if (next == chunk_end) { next = atomicAdd(counter, CHUNK); chunk_end = next + CHUNK; }
+            if (next >= n_samples) break;
+            start = next++ * GW_SSA_L;
+            pos = gw_ld32(ix.ssa[fm] + start / GW_SSA_L);
+            table[start / step] = (uint32_t)pos;
+            cursor = start; len = 0; mode = 1;
+        }
         cursor = gw_suffix_link(ix, fm, cursor);
+        ++len;
+        if ((cursor % GW_SSA_L) == 0) {   // the end of the walk
+            const uint32_t smp = gw_ld32(ix.ssa[fm] + cursor / GW_SSA_L);
+            if (mode == 1 && (u64)gw_ld32(ix.ssa[fm] + start / GW_SSA_L) != ((u64)smp + len) % N) {   // not a plain text walk: once more, the reference's way
+                redo_len = len; redo_smp = smp; cursor = start; len = 0; mode = 2;
+            } else
+                mode = 0;
+            continue;
+        }
+        if ((cursor & (step - 1u)) == 0) {
+            if (mode == 1) { pos = pos == 0 ? N - 1 : pos - 1; table[cursor / step] = (uint32_t)pos; }
+            else table[cursor / step] = (uint32_t)(((u64)redo_smp + (u64)(redo_len - len) + N) % N);
+        } else if (mode == 1)
+            pos = pos == 0 ? N - 1 : pos - 1;
     }
 }
 
@@ -493,8 +516,10 @@ void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const 
     else if (maxh <= 8) gw_flow_kernel<8><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<8>(), st>>>(env, slabs, active, n_active, work_counter, pp);
     else gw_flow_kernel<GW_MAX_ROWS><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<GW_MAX_ROWS>(), st>>>(env, slabs, active, n_active, work_counter, pp);
 }
-void gwk_densify(cudaStream_t st, const GwIndexView& ix, int fm, uint32_t step, uint32_t* table, uint32_t n_samples) {
-    if (n_samples) gw_densify_kernel<<<gw_grid(n_samples, 256), 256, 0, st>>>(ix, fm, step, table, n_samples);
+void gwk_densify(cudaStream_t st, const GwIndexView& ix, int fm, uint32_t step, uint32_t* table, uint32_t n_samples, uint32_t* counter) {
+    if (!n_samples) return;
+    const uint64_t want = ((uint64_t)n_samples + 255) / 256;   // persistent lanes: 8 CTAs of 256 per SM are plenty
+    gw_densify_kernel<<<(unsigned)std::min<uint64_t>(want, 148 * 8), 256, 0, st>>>(ix, fm, step, table, n_samples, counter);
 }
 void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count) {
     if (n) gw_collect_overflow_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, list, count);
