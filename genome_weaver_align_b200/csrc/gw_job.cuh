@@ -89,9 +89,8 @@ GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int nb_hint = 0) {
     gw_dp_forward(job->dp, env.cfg.band_width, job->peq, GwJobRef(job), gw_max(job->dp.bmax, nb_hint));
 }
 
-// traceback + CIGAR of the fragment whose forward pass is complete; results go to its pending-fragment record. seg: the lane's segment
-// buffer (shared memory in the flow kernel)
-GW_HD void gw_job_trace(const GwSearchEnv& env, const GwSlab& s, GwJob* job, uint32_t* seg, size_t stride, int nb_hint = 0) {
+// traceback + CIGAR of the fragment whose forward pass is complete; results go to its pending-fragment record
+GW_HD void gw_job_trace(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int nb_hint = 0) {
     GwReadCtx* c = s.ctx();
     GwPendFrag* pf = &c->pend[job->frag];
     const GwState* st = gw_st(s, pf->state_off);
@@ -106,14 +105,14 @@ GW_HD void gw_job_trace(const GwSearchEnv& env, const GwSlab& s, GwJob* job, uin
         return (int)((((qh >> (p & 63)) & 1ULL) << 1) | ((ql >> (p & 63)) & 1ULL));
     };
     GwVerifyOut out;
-    gw_dp_traceback(job->dp, env.cfg.band_width, job->peq, GwJobRef(job), qsym, seg, stride, gw_max(job->dp.bmax, nb_hint), pf->cig, &out);
+    gw_dp_traceback(job->dp, env.cfg.band_width, job->peq, GwJobRef(job), qsym, gw_max(job->dp.bmax, nb_hint), pf->cig, &out);
     pf->res_valid = out.valid; pf->res_pos = out.pos; pf->res_diff = out.diff; pf->res_cig_n = out.cig_n;
     if (out.cig_overflow) pf->res_abort = 2;  // cannot happen within GW_MAX_K; reported as unsupported
 }
 
 // whole verification of one pending fragment in one go (host simulator)
-GW_HD void gw_verify_frag(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag, uint32_t* seg, size_t stride) {
+GW_HD void gw_verify_frag(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag) {
     if (!gw_job_begin_dp(env, s, job, frag)) return;
     gw_job_columns(env, job);
-    gw_job_trace(env, s, job, seg, stride);
+    gw_job_trace(env, s, job);
 }

@@ -109,11 +109,10 @@ struct GwFlowParams {
     uint32_t flush;      // once the work list is drained, a partial verification batch runs when this many lanes idle
 };
 
-// dynamic shared memory of a CTA: the two FIFOs of every warp, the DP segment buffers (GW_DP_SEG_WORDS words per thread, lane-interleaved
-// per warp), then one GwLane record per thread (odd word stride)
+// dynamic shared memory of a CTA: the two FIFOs of every warp, then one GwLane record per thread (odd word stride)
 extern __shared__ uint32_t gw_flow_smem[];
 template <int MAXH>
-static size_t gw_flow_smem_bytes() { return ((size_t)2 * GW_WARPS * GW_RING + (size_t)GW_FLOW_THREADS * GW_DP_SEG_WORDS + (size_t)GW_FLOW_THREADS * GW_LANE_WORDS(MAXH)) * 4; }
+static size_t gw_flow_smem_bytes() { return ((size_t)2 * GW_WARPS * GW_RING + (size_t)GW_FLOW_THREADS * GW_LANE_WORDS(MAXH)) * 4; }
 
 template <int MAXH>
 __global__ void __launch_bounds__(GW_FLOW_THREADS, 2) gw_flow_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
@@ -123,8 +122,7 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, 2) gw_flow_kernel(GwSearchEnv
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t* ready = gw_flow_smem + wid * GW_RING;
     uint32_t* frags = gw_flow_smem + (GW_WARPS + wid) * GW_RING;
-    uint32_t* seg = gw_flow_smem + 2 * GW_WARPS * GW_RING + wid * 32 * GW_DP_SEG_WORDS + lane;   // word w of this lane: seg[w * 32]
-    GwLane<MAXH>& ln = *reinterpret_cast<GwLane<MAXH>*>(gw_flow_smem + 2 * GW_WARPS * GW_RING + GW_FLOW_THREADS * GW_DP_SEG_WORDS + threadIdx.x * GW_LANE_WORDS(MAXH));
+    GwLane<MAXH>& ln = *reinterpret_cast<GwLane<MAXH>*>(gw_flow_smem + 2 * GW_WARPS * GW_RING + threadIdx.x * GW_LANE_WORDS(MAXH));
     uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_pick = 0, age_cold = 0, owned = 0;
     bool drained = false;
     bool have = false;
@@ -161,7 +159,7 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, 2) gw_flow_kernel(GwSearchEnv
                 const int hint = (int)__reduce_max_sync(FULL, dp ? (unsigned)job.dp.bmax : 0u);
                 if (dp) gw_job_columns(env, &job, hint);
                 __syncwarp();
-                if (dp) gw_job_trace(env, sv, &job, seg, 32, hint);   // the recomputed segments are staged in the warp's shared-memory buffer
+                if (dp) gw_job_trace(env, sv, &job, hint);
             }
             __syncwarp();
             const uint32_t nid = __shfl_down_sync(FULL, id, 1);
@@ -449,14 +447,11 @@ __global__ void gw_scan_export_kernel(u64* const* slabs, uint32_t n, int strand,
     out[i * 5 + 3] = c->scan_lb[strand]; out[i * 5 + 4] = c->scan_ub[strand];
 }
 
-// alignBlockDetailed over explicit (ref, query) ASCII pairs (component entry point; also the DP-only profiling kernel). The segment
-// buffers are in shared memory, lane-interleaved, as in the flow kernel.
+// alignBlockDetailed over explicit (ref, query) ASCII pairs (component entry point; also the DP-only profiling kernel)
 __global__ void __launch_bounds__(128) gw_verify_pairs_kernel(const char* refs, const u64* ref_off, const char* queries, const u64* query_off, uint32_t n, int band_k,
                                        int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride) {
-    __shared__ uint32_t seg_s[128 * GW_DP_SEG_WORDS];
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    uint32_t* seg = seg_s + (threadIdx.x >> 5) * 32 * GW_DP_SEG_WORDS + (threadIdx.x & 31u);
     const char* r = refs + ref_off[i];
     const char* qs = queries + query_off[i];
     const int Ncols = (int)(ref_off[i + 1] - ref_off[i]);
@@ -473,7 +468,7 @@ __global__ void __launch_bounds__(128) gw_verify_pairs_kernel(const char* refs, 
     uint32_t cig[GW_CIG_CAP];
     GwVerifyOut out;
     GwDp d;
-    gw_verify(m, Ncols, band_k, peq, refsym, qsym, &d, seg, 32, cig, &out);
+    gw_verify(m, Ncols, band_k, peq, refsym, qsym, &d, cig, &out);
     result[i * 4 + 0] = out.valid; result[i * 4 + 1] = out.pos; result[i * 4 + 2] = out.diff;
     result[i * 4 + 3] = out.cig_overflow ? -1 : out.cig_n;
     for (int j = 0; j < out.cig_n && j < (int)cigar_stride; ++j) cigar_ops[(size_t)i * cigar_stride + j] = cig[j];

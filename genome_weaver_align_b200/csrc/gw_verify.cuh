@@ -5,19 +5,16 @@
 // (ops string, leading/trailing indel -> soft clip rewriting, run-length CIGAR).
 //
 // The reference keeps the VP/VN words of every (column, block) for the traceback: bMax x (N'+1) x 16 bytes per fragment. Here
-// nothing of that is kept in HBM. The forward pass stores only a checkpoint of its state every GW_DP_SEG columns (in the lane's
-// local memory); the traceback, which walks the columns downwards, recomputes the segment of GW_DP_SEG columns it is in from that
-// segment's checkpoint and stages what it needs of it in SHARED memory: for every column the 32 rows around the diagonal the
-// traceback started on (it cannot leave that band while the alignment has at most 15 differences: every row the path drifts from
-// the diagonal costs one) — 2 x 32 bits per column, 128 bytes per lane and segment. A row outside the band (an alignment with more
-// differences) is answered exactly by recomputing the one column it is in.
+// nothing of that is stored. The forward pass keeps one checkpoint of its state every GW_DP_SEG columns (a few hundred bytes in the
+// lane's local memory). The traceback needs a VP/VN bit only where the reference and query symbols differ (a handful of cells per
+// alignment: a matching cell is a diagonal step whatever the bits say); for such a cell the column is recomputed from the nearest
+// checkpoint — at most GW_DP_SEG + 1 column steps — and kept until the traceback leaves it.
 #pragma once
 #include "gw_fm.cuh"
 
 #define GW_RUN_CAP 64   // run-length encoded traceback ops kept per fragment (>= 2 * GW_MAX_K + 3)
-#define GW_DP_SEG 16    // columns per recomputed segment
+#define GW_DP_SEG 32    // columns between two checkpoints of the forward pass
 #define GW_DP_MAX_CK ((GW_MAX_WINDOW + GW_DP_SEG - 1) / GW_DP_SEG + 1)
-#define GW_DP_SEG_WORDS (2 * GW_DP_SEG)   // shared-memory words per lane: (VP band, VN band) per column of the segment
 
 struct GwVerifyOut {
     int valid;   // 0: reference returns null
@@ -144,54 +141,10 @@ GW_HD void gw_dp_forward_nb(GwDp& d, int band_k, const u64 (*peq)[GW_MAX_NB], Re
     d.has_best = hasBest ? 1 : 0; d.best_tail = bestTail; d.best_diff = bestDiff;
 }
 
-// 32 rows [lo, lo + 32) of a column given as blocks (rows outside [0, 64 * NB) read as 0)
-template <int NB>
-GW_HD uint32_t gw_dp_band(const u64 (&w)[NB], int lo) {
-    if (lo <= -32 || lo >= 64 * NB) return 0u;
-    if (lo < 0) return (uint32_t)(w[0] << (-lo));
-    const int b = lo >> 6, off = lo & 63;
-    u64 x0 = 0ULL, x1 = 0ULL;
-#pragma unroll
-    for (int r = 0; r < NB; ++r) { if (r == b) x0 = w[r]; if (r == b + 1) x1 = w[r]; }
-    return (uint32_t)((x0 >> off) | ((x1 << 1) << (63 - off)));
-}
-
-// Recomputes the columns [s * SEG, s * SEG + SEG] from the checkpoint of segment s and stages, for each column c of the segment, rows
-// [c + delta - 16, c + delta + 16) of what the reference's arrays hold for it (entry c + 1 of its VP/VN tables) in the segment buffer:
-// seg[(2 * e) * stride] = VP band, seg[(2 * e + 1) * stride] = VN band of column s * SEG + e. The column after the segment is
-// stepped too: when it switches a block on, the reference overwrites that block's entry of the column before.
+// What the reference's VP / VN tables hold for window column `col` (entry col + 1), as blocks: the columns from the checkpoint before
+// `col` up to col + 1 are stepped again (the column after `col` may switch a block on, which overwrites that block's entry of `col`)
 template <int NB, typename RefSym>
-GW_HD void gw_dp_segment_nb(const GwDp& d, int s, int delta, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, uint32_t* seg, size_t stride) {
-    const int m = d.m, bMax = d.bmax;
-    int D[NB], bCeil;
-    u64 vp[NB], vn[NB];
-    gw_dp_load<NB>(d.ck[s], D, vp, vn, bCeil);
-    const int j0 = s * GW_DP_SEG, j1 = gw_min(j0 + GW_DP_SEG + 1, d.ncols);
-    u64 sp[NB], sn[NB];   // the stored values of the previous column, held back one step for the overwrite
-    for (int j = j0; j < j1; ++j) {
-        int computed, activated;
-        gw_dp_step<NB>(D, vp, vn, bCeil, m, bMax, band_k, refsym(j), peq, &computed, &activated);
-        if (j > j0) {   // column j - 1 is final now
-#pragma unroll
-            for (int r = 0; r < NB; ++r) if (r == activated) { sp[r] = ~0ULL; sn[r] = 0ULL; }
-            const int e = j - 1 - j0, lo = (j - 1) + delta - 16;
-            seg[(size_t)(2 * e) * stride] = gw_dp_band<NB>(sp, lo);
-            seg[(size_t)(2 * e + 1) * stride] = gw_dp_band<NB>(sn, lo);
-        }
-#pragma unroll
-        for (int r = 0; r < NB; ++r) { const bool live = r < computed; sp[r] = live ? vp[r] : 0ULL; sn[r] = live ? vn[r] : 0ULL; }
-    }
-    if (j1 - j0 <= GW_DP_SEG && j1 > j0) {   // the window ended inside the segment: its last column has no successor
-        const int e = j1 - 1 - j0, lo = (j1 - 1) + delta - 16;
-        seg[(size_t)(2 * e) * stride] = gw_dp_band<NB>(sp, lo);
-        seg[(size_t)(2 * e + 1) * stride] = gw_dp_band<NB>(sn, lo);
-    }
-}
-
-// the VP / VN bits of (row, col) exactly, whatever the row: the segment's columns up to col + 1 are stepped again (rare: only rows
-// that left the staged band, i.e. alignments with more than 15 differences)
-template <int NB, typename RefSym>
-GW_HD void gw_dp_exact_nb(const GwDp& d, int col, int row, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, int* vpbit, int* vnbit) {
+GW_HD void gw_dp_column_nb(const GwDp& d, int col, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, u64* sp_out, u64* sn_out) {
     const int m = d.m, bMax = d.bmax;
     int D[NB], bCeil;
     u64 vp[NB], vn[NB];
@@ -212,12 +165,10 @@ GW_HD void gw_dp_exact_nb(const GwDp& d, int col, int row, int band_k, const u64
             for (int r = 0; r < NB; ++r) { const bool live = r < computed; sp[r] = live ? vp[r] : 0ULL; sn[r] = live ? vn[r] : 0ULL; }
         }
     }
-    const int b = row >> 6, off = row & 63;
-    u64 xp = 0ULL, xn = 0ULL;
 #pragma unroll
-    for (int r = 0; r < NB; ++r) if (r == b) { xp = sp[r]; xn = sn[r]; }
-    *vpbit = (int)((xp >> off) & 1ULL);
-    *vnbit = (int)((xn >> off) & 1ULL);
+    for (int r = 0; r < GW_MAX_NB; ++r) { sp_out[r] = 0ULL; sn_out[r] = 0ULL; }
+#pragma unroll
+    for (int r = 0; r < NB; ++r) { sp_out[r] = sp[r]; sn_out[r] = sn[r]; }
 }
 
 // nb: the instantiation to take (a caller whose lanes run together passes the largest block count among them, so that all of them take
@@ -229,23 +180,16 @@ GW_HD void gw_dp_forward(GwDp& d, int band_k, const u64 (*peq)[GW_MAX_NB], RefSy
     else gw_dp_forward_nb<GW_MAX_NB>(d, band_k, peq, refsym);
 }
 template <typename RefSym>
-GW_HD void gw_dp_segment(const GwDp& d, int s, int delta, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, uint32_t* seg, size_t stride, int nb) {
-    if (nb <= 1) gw_dp_segment_nb<1>(d, s, delta, band_k, peq, refsym, seg, stride);
-    else if (nb <= 2) gw_dp_segment_nb<2>(d, s, delta, band_k, peq, refsym, seg, stride);
-    else gw_dp_segment_nb<GW_MAX_NB>(d, s, delta, band_k, peq, refsym, seg, stride);
-}
-template <typename RefSym>
-GW_COLD void gw_dp_exact(const GwDp& d, int col, int row, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, int* vpbit, int* vnbit) {
-    if (d.bmax <= 1) gw_dp_exact_nb<1>(d, col, row, band_k, peq, refsym, vpbit, vnbit);
-    else if (d.bmax <= 2) gw_dp_exact_nb<2>(d, col, row, band_k, peq, refsym, vpbit, vnbit);
-    else gw_dp_exact_nb<GW_MAX_NB>(d, col, row, band_k, peq, refsym, vpbit, vnbit);
+GW_HD void gw_dp_column(const GwDp& d, int col, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, u64* sp, u64* sn, int nb) {
+    if (nb <= 1) gw_dp_column_nb<1>(d, col, band_k, peq, refsym, sp, sn);
+    else if (nb <= 2) gw_dp_column_nb<2>(d, col, band_k, peq, refsym, sp, sn);
+    else gw_dp_column_nb<GW_MAX_NB>(d, col, band_k, peq, refsym, sp, sn);
 }
 
-// traceback (:529-595) + CIGAR (:599-644). refsym / qsym: symbols of the window columns / query rows; seg: the lane's segment buffer in
-// shared memory (GW_DP_SEG_WORDS words at `stride`); nb: instantiation of the recomputation (see gw_dp_forward)
+// traceback (:529-595) + CIGAR (:599-644). refsym / qsym: symbols of the window columns / query rows; nb: instantiation of the
+// recomputation (see gw_dp_forward)
 template <typename RefSym, typename QSym>
-GW_HD void gw_dp_traceback(const GwDp& d, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, QSym qsym, uint32_t* seg, size_t stride, int nb,
-                           uint32_t* cig_out, GwVerifyOut* out) {
+GW_HD void gw_dp_traceback(const GwDp& d, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, QSym qsym, int nb, uint32_t* cig_out, GwVerifyOut* out) {
     const int m = d.m;
     const bool hasBest = d.has_best != 0;
     const int bestTail = d.best_tail;
@@ -263,25 +207,20 @@ GW_HD void gw_dp_traceback(const GwDp& d, int band_k, const u64 (*peq)[GW_MAX_NB
     };
     int leftMostPos = 0, diff = 0;
     int col = bestTail, row = m - 1;
-    const int delta = row - col;   // the diagonal the traceback starts on
-    int have_seg = -1;
+    int have_col = -1;
+    u64 sp[GW_MAX_NB], sn[GW_MAX_NB];   // the column the traceback is in, recomputed when a cell needs its bits
     for (;;) {
         int path = 0;
         if (col >= 0 && row >= 0) {
             if (refsym(col) == qsym(row)) path = 1;
             else {
-                int vpb, vnb;
-                const int rel = row - (col + delta - 16);
-                if (rel >= 0 && rel < 32) {
-                    const int s = col / GW_DP_SEG;
-                    if (s != have_seg) { gw_dp_segment(d, s, delta, band_k, peq, refsym, seg, stride, nb); have_seg = s; }
-                    const int e = col - s * GW_DP_SEG;
-                    vpb = (int)((seg[(size_t)(2 * e) * stride] >> rel) & 1u);
-                    vnb = (int)((seg[(size_t)(2 * e + 1) * stride] >> rel) & 1u);
-                } else
-                    gw_dp_exact(d, col, row, band_k, peq, refsym, &vpb, &vnb);
-                if (vpb) path = 3;
-                else if (!vnb) path = 2;
+                if (col != have_col) { gw_dp_column(d, col, band_k, peq, refsym, sp, sn, nb); have_col = col; }
+                const int b = row >> 6, off = row & 63;
+                u64 xp = 0ULL, xn = 0ULL;
+#pragma unroll
+                for (int r = 0; r < GW_MAX_NB; ++r) if (r == b) { xp = sp[r]; xn = sn[r]; }
+                if ((xp >> off) & 1ULL) path = 3;
+                else if (!((xn >> off) & 1ULL)) path = 2;
                 else path = 4;
                 diff++;
             }
@@ -330,9 +269,8 @@ GW_HD void gw_dp_traceback(const GwDp& d, int band_k, const u64 (*peq)[GW_MAX_NB
 
 // alignBlockDetailed in one go (component entry point, host simulator)
 template <typename RefSym, typename QSym>
-GW_HD void gw_verify(int m, int Ncols, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, QSym qsym, GwDp* d, uint32_t* seg, size_t stride,
-                     uint32_t* cig_out, GwVerifyOut* out) {
+GW_HD void gw_verify(int m, int Ncols, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, QSym qsym, GwDp* d, uint32_t* cig_out, GwVerifyOut* out) {
     d->m = m; d->ncols = Ncols; d->bmax = gw_max(1, (m + 63) / 64);
     gw_dp_forward(*d, band_k, peq, refsym, d->bmax);
-    gw_dp_traceback(*d, band_k, peq, refsym, qsym, seg, stride, d->bmax, cig_out, out);
+    gw_dp_traceback(*d, band_k, peq, refsym, qsym, d->bmax, cig_out, out);
 }

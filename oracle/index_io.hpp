@@ -45,7 +45,7 @@ static inline bool snappyUncompress(const uint8_t* in, size_t n, std::vector<uin
         shift += 7;
     }
     size_t base = out.size();
-    out.reserve(base + ulen);
+    if (out.capacity() < base + ulen) out.reserve(std::max(base + ulen, out.capacity() * 2));   // geometric: the loaders append chunk after chunk
     while (p < n) {
         uint8_t tag = in[p++];
         int type = tag & 3;
@@ -118,6 +118,7 @@ static inline ACGTSequence loadACGTSequence(const std::string& path) {
     size_t p = 8;
     if (d.size() >= p + 16 && memcmp(d.data() + p, SNAPPY_MAGIC, 8) == 0) p += 16;
     std::vector<uint8_t> raw;
+    raw.reserve((size_t)ACGTSequence::minArraySize(numBases) * 8 + 64);
     while (p + 4 <= d.size()) {
         uint32_t clen = getBE32(d.data() + p);
         p += 4;
