@@ -15,7 +15,7 @@ GW_HD u64 gw_plane_window(const u64* plane, uint32_t n_words, uint32_t p) {
 }
 
 // AlignmentProcess.verify, window + query set-up (:517-538); returns false when the fragment is finished without a DP
-GW_COLD bool gw_job_begin_dp(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag) {
+GW_COLD bool gw_job_begin_dp(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag, GwU64x2* hist, size_t stride) {
     GwReadCtx* c = s.ctx();
     job->frag = frag;
     GwPendFrag* pf = &c->pend[frag];
@@ -60,7 +60,9 @@ GW_COLD bool gw_job_begin_dp(const GwSearchEnv& env, const GwSlab& s, GwJob* job
         job->rw_hi[w] = gw_plane_window(ix.ref_hi, n_words, p);
         job->rw_nf[w] = gw_plane_window(ix.ref_nf, n_words, p);
     }
-    job->dp.m = fragLen; job->dp.ncols = Ncols; job->dp.bmax = gw_max(1, (fragLen + 63) / 64);
+    GwDp d;
+    gw_dp_begin(d, fragLen, Ncols, env.cfg.band_width, hist, stride);
+    job->dp = d;
     return true;
 }
 
@@ -70,49 +72,52 @@ GW_HD int gw_job_ref_symbol(const GwJob* job, int j) {
     return (int)((((job->rw_hi[w] >> sft) & 1ULL) << 1) | ((job->rw_lo[w] >> sft) & 1ULL));
 }
 
-// reference symbol of window column j from the job's planes (columns advance one by one: the words are reloaded every 64 columns only)
-struct GwJobRef {
-    const GwJob* job;
-    int rw;
-    u64 rl, rh, rn;
-    GW_HD explicit GwJobRef(const GwJob* j) : job(j), rw(-1), rl(0), rh(0), rn(0) {}
-    GW_HD int operator()(int j) {
-        if ((j >> 6) != rw) { rw = j >> 6; rl = job->rw_lo[rw]; rh = job->rw_hi[rw]; rn = job->rw_nf[rw]; }
-        const int sft = j & 63;
-        if ((rn >> sft) & 1ULL) return 4;
-        return (int)((((rh >> sft) & 1ULL) << 1) | ((rl >> sft) & 1ULL));
-    }
-};
-
-// forward pass over the window columns of a job (best end column + segment checkpoints, nothing stored per column)
-GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int nb_hint = 0) {
-    gw_dp_forward(job->dp, env.cfg.band_width, job->peq, GwJobRef(job), gw_max(job->dp.bmax, nb_hint));
-}
-
-// traceback + CIGAR of the fragment whose forward pass is complete; results go to its pending-fragment record
-GW_HD void gw_job_trace(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int nb_hint = 0) {
+// traceback + CIGAR of the fragment whose DP is complete; results go to its pending-fragment record
+GW_HD void gw_job_trace(const GwSlab& s, GwJob* job, const GwU64x2* hist, size_t stride) {
     GwReadCtx* c = s.ctx();
     GwPendFrag* pf = &c->pend[job->frag];
     const GwState* st = gw_st(s, pf->state_off);
     const int strand = gw_strand(st), start = st->start, end = st->end;
     const u64* qlo = c->qlo[strand];
     const u64* qhi = c->qhi[strand];
-    // the traceback moves through rows one at a time: keep the 64-symbol word it is in
+    // the traceback moves through rows and columns one at a time: keep the 64-symbol words it is in
     int qw = -1; u64 ql = 0, qh = 0;
     auto qsym = [&](int i) -> int {
         const int p = strand == 0 ? start + i : end - 1 - i;
         if ((p >> 6) != qw) { qw = p >> 6; ql = qlo[qw]; qh = qhi[qw]; }
         return (int)((((qh >> (p & 63)) & 1ULL) << 1) | ((ql >> (p & 63)) & 1ULL));
     };
+    int rw = -1; u64 rl = 0, rh = 0, rn = 0;
+    auto refsym = [&](int j) -> int {
+        if ((j >> 6) != rw) { rw = j >> 6; rl = job->rw_lo[rw]; rh = job->rw_hi[rw]; rn = job->rw_nf[rw]; }
+        const int sft = j & 63;
+        if ((rn >> sft) & 1ULL) return 4;
+        return (int)((((rh >> sft) & 1ULL) << 1) | ((rl >> sft) & 1ULL));
+    };
     GwVerifyOut out;
-    gw_dp_traceback(job->dp, env.cfg.band_width, job->peq, GwJobRef(job), qsym, gw_max(job->dp.bmax, nb_hint), pf->cig, &out);
+    gw_dp_traceback(job->dp, refsym, qsym, hist, stride, pf->cig, &out);
     pf->res_valid = out.valid; pf->res_pos = out.pos; pf->res_diff = out.diff; pf->res_cig_n = out.cig_n;
     if (out.cig_overflow) pf->res_abort = 2;  // cannot happen within GW_MAX_K; reported as unsupported
 }
 
-// whole verification of one pending fragment in one go (host simulator)
-GW_HD void gw_verify_frag(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag) {
-    if (!gw_job_begin_dp(env, s, job, frag)) return;
-    gw_job_columns(env, job);
-    gw_job_trace(env, s, job);
+// DP columns [d.j, jEnd) of a job
+GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int n_cols, GwU64x2* hist, size_t stride, int nb_hint = 0) {
+    GwDp d = job->dp;
+    int rw = -1; u64 rl = 0, rh = 0, rn = 0;
+    auto refsym = [&](int j) -> int {   // columns advance one by one: reload the window words every 64 columns only
+        if ((j >> 6) != rw) { rw = j >> 6; rl = job->rw_lo[rw]; rh = job->rw_hi[rw]; rn = job->rw_nf[rw]; }
+        const int sft = j & 63;
+        if ((rn >> sft) & 1ULL) return 4;
+        return (int)((((rh >> sft) & 1ULL) << 1) | ((rl >> sft) & 1ULL));
+    };
+    gw_dp_columns(d, d.j + n_cols, env.cfg.band_width, job->peq, refsym, hist, stride, nb_hint);
+    job->dp = d;
 }
+
+// whole verification of one pending fragment in one go (pool kernel: the job lives in the lane's local memory)
+GW_HD void gw_verify_frag(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag, GwU64x2* hist, size_t stride) {
+    if (!gw_job_begin_dp(env, s, job, frag, hist, stride)) return;
+    gw_job_columns(env, job, job->dp.ncols, hist, stride);
+    gw_job_trace(s, job, hist, stride);
+}
+

@@ -8,7 +8,7 @@ void gwk_fill_slab_ptrs(cudaStream_t st, u64** slabs, u64* base, size_t slab_wor
 void gwk_prep(cudaStream_t st, const GwBatchView& bv, u64* const* slabs, const uint32_t* slots, uint32_t n, uint32_t read_base, const GwSlabParams& sp);
 void gwk_scan(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* slots, uint32_t n_slots, int coop);
 void gwk_flow_setup(void);   // per-device function attributes of the flow kernel
-void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter,
+void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
               uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh);
 void gwk_densify(cudaStream_t st, const GwIndexView& ix, int fm, uint32_t step, uint32_t* table /* ceil(N / step), preset to 0xFF */, uint32_t n_samples,
                  uint32_t* counter /* device word, zero */);
@@ -25,4 +25,4 @@ void gwk_rank_acgtn(cudaStream_t st, const GwIndexView& ix, int which, const uin
 void gwk_locate_rows(cudaStream_t st, const GwIndexView& ix, int which, const uint32_t* rows, uint32_t n, uint32_t* out);
 void gwk_scan_export(cudaStream_t st, u64* const* slabs, uint32_t n, int strand, uint32_t* out);
 void gwk_verify_pairs(cudaStream_t st, const char* refs, const u64* ref_off, const char* queries, const u64* query_off, uint32_t n, int band_k,
-                      int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride);
+                      int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride, void* hist, uint32_t max_m);

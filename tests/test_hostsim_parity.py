@@ -123,8 +123,8 @@ def test_verifier_body_against_oracle():
 
 
 def test_verifier_many_differences_and_unrelated_windows():
-    # alignments that leave the band staged for the traceback (more than 15 differences), unrelated windows, windows shorter than the
-    # query: the recomputing verifier must still give what alignBlockDetailed gives
+    # alignments with dozens of differences, unrelated windows, windows shorter than the query: the device verifier body must still give
+    # what alignBlockDetailed gives
     import random
     rnd_ = random.Random(11)
     for t in range(400):
