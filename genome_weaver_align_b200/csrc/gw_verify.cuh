@@ -10,6 +10,25 @@
 
 #define GW_RUN_CAP 64   // run-length encoded traceback ops kept per fragment (>= 2 * GW_MAX_K + 3)
 
+// The history is written once and read at most once (by the traceback, minutes of GPU time later in cache terms): its stores and loads
+// carry the streaming hint, so that they do not push the work areas of the searching reads out of the L2.
+GW_HD void gw_hist_put(GwU64x2* p, u64 vp, u64 vn) {
+#if defined(__CUDA_ARCH__)
+    __stcs(reinterpret_cast<ulonglong2*>(p), make_ulonglong2(vp, vn));
+#else
+    p->x = vp; p->y = vn;
+#endif
+}
+GW_HD GwU64x2 gw_hist_get(const GwU64x2* p) {
+#if defined(__CUDA_ARCH__)
+    const ulonglong2 v = __ldcs(reinterpret_cast<const ulonglong2*>(p));
+    GwU64x2 r; r.x = v.x; r.y = v.y;
+    return r;
+#else
+    return *p;
+#endif
+}
+
 struct GwVerifyOut {
     int valid;   // 0: reference returns null
     int pos, diff, cig_n;
@@ -33,7 +52,7 @@ GW_HD void gw_dp_begin(GwDp& d, int m, int Ncols, int band_k, GwU64x2* hist, siz
 #pragma unroll
     for (int r = 0; r < GW_MAX_NB; ++r) { d.D[r] = 0; d.vp[r] = ~0ULL; d.vn[r] = 0ULL; }
     d.D[0] = m;
-    for (int r = 0; r < d.bmax; ++r) hist[(size_t)r * stride] = GwU64x2{~0ULL, 0ULL};  // column 0
+    for (int r = 0; r < d.bmax; ++r) gw_hist_put(&hist[(size_t)r * stride], ~0ULL, 0ULL);  // column 0
     d.bceil = gw_max(1, (band_k + 63) / 64);
     if (d.bceil > d.bmax) d.bceil = d.bmax;  // band_k <= 64 in practice; keeps indices in range
     d.has_best = 0; d.best_tail = -1; d.best_diff = 0;
@@ -73,7 +92,7 @@ GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_M
                 if (carry > 0) hp2 |= 1ULL;
                 vp[r] = hn2 | ~(d0 | hp2);
                 vn[r] = d0 & hp2;
-                col[(size_t)r * stride] = GwU64x2{vp[r], vn[r]};
+                gw_hist_put(&col[(size_t)r * stride], vp[r], vn[r]);
                 D[r] += hout;
                 carry = hout;
             }
@@ -86,7 +105,7 @@ GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_M
                 u64 x = ch < 4 ? peq[ch][r] : 0ULL;
                 if (D[r - 1] - carry <= gw_score_boundary(m, band_k, r - 1) && (((x & 1ULL) != 0ULL) | (carry < 0))) {
                     // vp[r][j] = ~0, vn[r][j] = 0 ; then one block step
-                    hist[((size_t)j * bMax + r) * stride] = GwU64x2{~0ULL, 0ULL};
+                    gw_hist_put(&hist[((size_t)j * bMax + r) * stride], ~0ULL, 0ULL);
                     u64 vpr = ~0ULL, vnr = 0ULL;
                     if (carry < 0) x |= 1ULL;
                     u64 d0 = (((x & vpr) + vpr) ^ vpr) | x | vnr;
@@ -98,7 +117,7 @@ GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_M
                     if (carry > 0) hp2 |= 1ULL;
                     vp[r] = hn2 | ~(d0 | hp2);
                     vn[r] = d0 & hp2;
-                    col[(size_t)r * stride] = GwU64x2{vp[r], vn[r]};
+                    gw_hist_put(&col[(size_t)r * stride], vp[r], vn[r]);
                     D[r] = D[r - 1] - carry + hout;
                     bCeil = r + 1;
                     computed = bCeil;
@@ -115,7 +134,7 @@ GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_M
         // (a block deactivated just now was computed and keeps its values, as in the reference)
 #pragma unroll
         for (int r = 1; r < NB; ++r)
-            if (r >= computed && r < bMax) col[(size_t)r * stride] = GwU64x2{0ULL, 0ULL};
+            if (r >= computed && r < bMax) gw_hist_put(&col[(size_t)r * stride], 0ULL, 0ULL);
         if (bCeil == bMax) {
             int dl = D[0];
 #pragma unroll
@@ -165,7 +184,7 @@ GW_HD void gw_dp_traceback(const GwDp& d, RefSym refsym, QSym qsym, const GwU64x
         int path = 0;
         if (col >= 0 && row >= 0) {
             const int block = row >> 6, offset = row & 63;
-            if (col != hcol || block != hblk) { v = hist[((size_t)(col + 1) * bMax + block) * stride]; hcol = col; hblk = block; }
+            if (col != hcol || block != hblk) { v = gw_hist_get(&hist[((size_t)(col + 1) * bMax + block) * stride]); hcol = col; hblk = block; }
             if (refsym(col) == qsym(row)) path = 1;
             else if ((v.x >> offset) & 1ULL) { path = 3; diff++; }
             else if (!((v.y >> offset) & 1ULL)) { path = 2; diff++; }
