@@ -107,7 +107,6 @@ struct GwFlowParams {
     uint32_t batch;      // lanes that must wait for a deferred continuation before the warp runs it
     uint32_t age;        // ... or this many trips since the first lane started waiting
     uint32_t flush;      // once the work list is drained, a partial verification batch runs when this many lanes idle
-    uint32_t own;        // reads a warp has taken from the work list and not finished, at most (<= GW_RING): what is in flight has to fit the L2
 };
 
 // dynamic shared memory of a CTA: the two FIFOs of every warp, then one GwLane record per thread (odd word stride)
@@ -178,7 +177,7 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, 2) gw_flow_kernel(GwSearchEnv
             if ((uint32_t)__popc(idle) >= pp.batch || busy == 0u || ++age_pick >= pp.age) {
                 age_pick = 0;
                 uint32_t nrd = n_ready;
-                if (nrd < (uint32_t)__popc(idle) && !drained && owned + pp.cap <= pp.own) {
+                if (nrd < (uint32_t)__popc(idle) && !drained && owned + pp.cap <= GW_RING) {
                     uint32_t first = 0;
                     if (lane == 0) first = atomicAdd(work_counter, pp.cap);
                     first = __shfl_sync(FULL, first, 0);
@@ -504,10 +503,9 @@ void gwk_flow_setup(void) {   // function attributes are per device: called once
     gw_flow_attr<4>(); gw_flow_attr<8>(); gw_flow_attr<GW_MAX_ROWS>();
 }
 void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-              uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t own, uint32_t blocks, int maxh) {
+              uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh) {
     if (!n_active) return;
     GwFlowParams pp;
-    pp.own = own < 32 ? 32 : (own > GW_RING ? GW_RING : own);
     pp.cap = fetch < 1 ? 1 : (fetch > 32 ? 32 : fetch);
     pp.batch = batch < 1 ? 1 : batch; pp.age = age < 1 ? 1 : age; pp.flush = flush < 1 ? 1 : flush;
     GwU64x2* h = (GwU64x2*)hist;

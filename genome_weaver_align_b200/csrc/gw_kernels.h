@@ -9,7 +9,7 @@ void gwk_prep(cudaStream_t st, const GwBatchView& bv, u64* const* slabs, const u
 void gwk_scan(cudaStream_t st, const GwIndexView& ix, u64* const* slabs, const uint32_t* slots, uint32_t n_slots, int coop);
 void gwk_flow_setup(void);   // per-device function attributes of the flow kernel
 void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const uint32_t* active, uint32_t n_active, uint32_t* work_counter, void* hist,
-              uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t own, uint32_t blocks, int maxh);
+              uint32_t fetch, uint32_t batch, uint32_t age, uint32_t flush, uint32_t blocks, int maxh);
 void gwk_densify(cudaStream_t st, const GwIndexView& ix, int fm, uint32_t step, uint32_t* table /* ceil(N / step), preset to 0xFF */, uint32_t n_samples,
                  uint32_t* counter /* device word, zero */);
 void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count);
