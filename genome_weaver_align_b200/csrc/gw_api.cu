@@ -18,6 +18,7 @@
 #include "gw_kernels.h"
 
 static_assert(sizeof(gw_hit_t) == sizeof(GwHitRec), "gw_hit_t and the device record must have the same layout");
+static_assert(GW_VERIFY_PAIRS_NOALLOC_MAX_BYTES == GW_NOALLOC_SCRATCH_BYTES, "header and gw_noalloc.cu disagree on the scratch size");
 static_assert(GW_CHR_NULL == GW_CHR_NULL_ && GW_CHR_EMPTY == GW_CHR_EMPTY_ && GW_CHR_STAR == GW_CHR_STAR_, "chr id constants");
 
 bool gw_sam_one(const std::vector<GwContig>& ctg, const std::string& name, const char* bases, size_t m, const char* qual, size_t qlen,
