@@ -65,7 +65,7 @@ SYMBOLS = {
     "gw_locate": (C.c_int, [_P, C.c_int, _P, C.c_uint32, _P]),
     "gw_quick_scan": (C.c_int, [_P, _P, _P, C.c_uint32, C.c_int, C.c_int, _P]),
     "gw_verify_pairs": (C.c_int, [C.c_int, _P, _P, _P, _P, C.c_uint32, C.c_int, _P, _P, C.c_uint32]),
-    "gw_verify_pairs_noalloc": (C.c_int, [C.c_int, _P, _P, _P, _P, _P, C.c_uint32, C.c_uint32, C.c_int, _P, _P, C.c_uint32]),
+    "gw_verify_pairs_noalloc": (C.c_int, [C.c_int, _P, _P, _P, _P, _P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, _P, _P, C.c_uint32]),
     "gw_staircase_table": (C.c_int, [C.c_int, C.c_int, C.c_int, _P, C.c_int]),
     "gw_cyclic_suffix_array": (C.c_int, [_P, C.c_uint64, C.c_int, _P]),
     "gw_max_edit_distance_c": (C.c_int, [C.c_float, C.c_int]),

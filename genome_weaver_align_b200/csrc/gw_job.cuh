@@ -15,7 +15,7 @@ GW_HD u64 gw_plane_window(const u64* plane, uint32_t n_words, uint32_t p) {
 }
 
 // AlignmentProcess.verify, window + query set-up (:517-538); returns false when the fragment is finished without a DP
-GW_COLD bool gw_job_begin_dp(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag, u64* hist, size_t stride) {
+GW_COLD bool gw_job_begin_dp(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag, GwU64x2* hist, size_t stride) {
     GwReadCtx* c = s.ctx();
     job->frag = frag;
     GwPendFrag* pf = &c->pend[frag];
@@ -73,7 +73,7 @@ GW_HD int gw_job_ref_symbol(const GwJob* job, int j) {
 }
 
 // traceback + CIGAR of the fragment whose DP is complete; results go to its pending-fragment record
-GW_HD void gw_job_trace(const GwSearchEnv& env, const GwSlab& s, GwJob* job, const u64* hist, size_t stride) {
+GW_HD void gw_job_trace(const GwSlab& s, GwJob* job, const GwU64x2* hist, size_t stride) {
     GwReadCtx* c = s.ctx();
     GwPendFrag* pf = &c->pend[job->frag];
     const GwState* st = gw_st(s, pf->state_off);
@@ -95,13 +95,13 @@ GW_HD void gw_job_trace(const GwSearchEnv& env, const GwSlab& s, GwJob* job, con
         return (int)((((rh >> sft) & 1ULL) << 1) | ((rl >> sft) & 1ULL));
     };
     GwVerifyOut out;
-    gw_dp_traceback(job->dp, env.cfg.band_width, job->peq, refsym, qsym, hist, stride, pf->cig, &out);
+    gw_dp_traceback(job->dp, refsym, qsym, hist, stride, pf->cig, &out);
     pf->res_valid = out.valid; pf->res_pos = out.pos; pf->res_diff = out.diff; pf->res_cig_n = out.cig_n;
     if (out.cig_overflow) pf->res_abort = 2;  // cannot happen within GW_MAX_K; reported as unsupported
 }
 
 // DP columns [d.j, jEnd) of a job
-GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int n_cols, u64* hist, size_t stride, int nb_hint = 0) {
+GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int n_cols, GwU64x2* hist, size_t stride, int nb_hint = 0) {
     GwDp d = job->dp;
     int rw = -1; u64 rl = 0, rh = 0, rn = 0;
     auto refsym = [&](int j) -> int {   // columns advance one by one: reload the window words every 64 columns only
@@ -115,9 +115,9 @@ GW_HD void gw_job_columns(const GwSearchEnv& env, GwJob* job, int n_cols, u64* h
 }
 
 // whole verification of one pending fragment in one go (pool kernel: the job lives in the lane's local memory)
-GW_HD void gw_verify_frag(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag, u64* hist, size_t stride) {
+GW_HD void gw_verify_frag(const GwSearchEnv& env, const GwSlab& s, GwJob* job, int frag, GwU64x2* hist, size_t stride) {
     if (!gw_job_begin_dp(env, s, job, frag, hist, stride)) return;
     gw_job_columns(env, job, job->dp.ncols, hist, stride);
-    gw_job_trace(env, s, job, hist, stride);
+    gw_job_trace(s, job, hist, stride);
 }
 

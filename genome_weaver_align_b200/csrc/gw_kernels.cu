@@ -116,7 +116,7 @@ static size_t gw_flow_smem_bytes() { return ((size_t)2 * GW_WARPS * GW_RING + (s
 
 template <int MAXH>
 __global__ void __launch_bounds__(GW_FLOW_THREADS, 2) gw_flow_kernel(GwSearchEnv env, u64* const* slabs, const uint32_t* active, uint32_t n_active,
-                                                                  uint32_t* work_counter, u64* hist, GwFlowParams pp) {
+                                                                  uint32_t* work_counter, GwU64x2* hist, GwFlowParams pp) {
     const uint32_t FULL = 0xFFFFFFFFu, MASK = GW_RING - 1u;
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, 2) gw_flow_kernel(GwSearchEnv
     uint32_t* frags = gw_flow_smem + (GW_WARPS + wid) * GW_RING;
     GwLane<MAXH>& ln = *reinterpret_cast<GwLane<MAXH>*>(gw_flow_smem + 2 * GW_WARPS * GW_RING + threadIdx.x * GW_LANE_WORDS(MAXH));
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    u64* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    GwU64x2* my_hist = hist + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t r_head = 0, r_tail = 0, f_head = 0, f_tail = 0, age_pick = 0, age_cold = 0, owned = 0;
     bool drained = false;
     bool have = false;
@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, 2) gw_flow_kernel(GwSearchEnv
                 const int hint = (int)__reduce_max_sync(FULL, dp ? (unsigned)job.dp.bmax : 0u);
                 if (dp) gw_job_columns(env, &job, job.dp.ncols, my_hist, stride, hint);
                 __syncwarp();
-                if (dp) gw_job_trace(env, sv, &job, my_hist, stride);
+                if (dp) gw_job_trace(sv, &job, my_hist, stride);
             }
             __syncwarp();
             const uint32_t nid = __shfl_down_sync(FULL, id, 1);
@@ -451,7 +451,7 @@ __global__ void gw_scan_export_kernel(u64* const* slabs, uint32_t n, int strand,
 
 // alignBlockDetailed over explicit (ref, query) ASCII pairs
 __global__ void gw_verify_pairs_kernel(const char* refs, const u64* ref_off, const char* queries, const u64* query_off, uint32_t n, int band_k,
-                                       int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride, u64* hist, uint32_t max_m) {
+                                       int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride, GwU64x2* hist, uint32_t max_m) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const char* r = refs + ref_off[i];
@@ -508,7 +508,7 @@ void gwk_flow(cudaStream_t st, const GwSearchEnv& env, u64* const* slabs, const 
     GwFlowParams pp;
     pp.cap = fetch < 1 ? 1 : (fetch > 32 ? 32 : fetch);
     pp.batch = batch < 1 ? 1 : batch; pp.age = age < 1 ? 1 : age; pp.flush = flush < 1 ? 1 : flush;
-    u64* h = (u64*)hist;
+    GwU64x2* h = (GwU64x2*)hist;
     if (maxh <= 4) gw_flow_kernel<4><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<4>(), st>>>(env, slabs, active, n_active, work_counter, h, pp);
     else if (maxh <= 8) gw_flow_kernel<8><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<8>(), st>>>(env, slabs, active, n_active, work_counter, h, pp);
     else gw_flow_kernel<GW_MAX_ROWS><<<blocks, GW_FLOW_THREADS, gw_flow_smem_bytes<GW_MAX_ROWS>(), st>>>(env, slabs, active, n_active, work_counter, h, pp);
@@ -579,5 +579,5 @@ void gwk_scan_export(cudaStream_t st, u64* const* slabs, uint32_t n, int strand,
 }
 void gwk_verify_pairs(cudaStream_t st, const char* refs, const u64* ref_off, const char* queries, const u64* query_off, uint32_t n, int band_k,
                       int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride, void* hist, uint32_t max_m) {
-    if (n) gw_verify_pairs_kernel<<<gw_grid(n, 128), 128, 0, st>>>(refs, ref_off, queries, query_off, n, band_k, result, cigar_ops, cigar_stride, (u64*)hist, max_m);
+    if (n) gw_verify_pairs_kernel<<<gw_grid(n, 128), 128, 0, st>>>(refs, ref_off, queries, query_off, n, band_k, result, cigar_ops, cigar_stride, (GwU64x2*)hist, max_m);
 }

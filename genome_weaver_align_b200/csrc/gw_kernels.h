@@ -27,10 +27,10 @@ void gwk_scan_export(cudaStream_t st, u64* const* slabs, uint32_t n, int strand,
 void gwk_verify_pairs(cudaStream_t st, const char* refs, const u64* ref_off, const char* queries, const u64* query_off, uint32_t n, int band_k,
                       int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride, void* hist, uint32_t max_m);
 // gw_noalloc.cu: the pair verifier with its DP history in a static __device__ array (no allocation anywhere on the call path)
-#define GW_NOALLOC_SCRATCH_BYTES (32u << 20)
+#define GW_NOALLOC_SCRATCH_BYTES (64u << 20)
 #ifndef GW_NOALLOC_PAIR_TOO_LONG
 #define GW_NOALLOC_PAIR_TOO_LONG (-2)
 #endif
-size_t gwk_verify_pairs_noalloc_need(uint32_t n, uint32_t max_cols);
+size_t gwk_verify_pairs_noalloc_need(uint32_t n, uint32_t max_cols, uint32_t max_m);
 cudaError_t gwk_verify_pairs_noalloc(cudaStream_t st, const char* refs, const u64* ref_off, const char* queries, const u64* query_off, uint32_t n,
-                                     uint32_t max_cols, int band_k, int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride);
+                                     uint32_t max_cols, uint32_t max_m, int band_k, int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride);

@@ -3,47 +3,31 @@
 // align/src/main/java/org/utgenome/weaver/align/BitParallelSmithWaterman.java): align :387-459 (block-wise Myers /
 // Hyyro recurrence with adaptive number of active 64-row blocks), alignBlock :461-491, traceback :501-644
 // (ops string, leading/trailing indel -> soft clip rewriting, run-length CIGAR).
-// The traceback needs the VP / VN bit of (row, column) only near the diagonal the alignment runs on: every row it drifts from the
-// diagonal it started on costs one difference. So of the reference's history (bMax x (N'+1) words of VP and of VN) only a band of 32
-// rows around the window's main diagonal is kept per column — 2 x 32 bits, one 8-byte word, laid out [column][request] so that the 32
-// lanes of a warp write 256 contiguous bytes per column: a quarter of the bytes for a 100 bp read, an eighth for 250 bp. A cell
-// outside the band (an alignment that wanders more than 16 rows off the diagonal: more differences than any accepted alignment
-// has) is answered exactly by replaying the recurrence up to its column (gw_dp_replay, out of line).
+// The VP/VN history needed by the traceback (bMax x (N'+1) words each) is staged in a scratch area laid out
+// [column][block][request] so that the 32 lanes of a warp write 512 contiguous bytes per (column, block).
 #pragma once
 #include "gw_fm.cuh"
 
 #define GW_RUN_CAP 64   // run-length encoded traceback ops kept per fragment (>= 2 * GW_MAX_K + 3)
 
-// The history is written once and read at most once, much later in cache terms: its stores and loads carry the streaming hint.
-GW_HD void gw_hist_put(u64* p, uint32_t vpband, uint32_t vnband) {
-    const u64 v = (u64)vpband | ((u64)vnband << 32);
+// The history is written once and read at most once (by the traceback, minutes of GPU time later in cache terms): its stores and loads
+// carry the streaming hint, so that they do not push the work areas of the searching reads out of the L2.
+GW_HD void gw_hist_put(GwU64x2* p, u64 vp, u64 vn) {
 #if defined(__CUDA_ARCH__)
-    __stcs(p, v);
+    __stcs(reinterpret_cast<ulonglong2*>(p), make_ulonglong2(vp, vn));
 #else
-    *p = v;
+    p->x = vp; p->y = vn;
 #endif
 }
-GW_HD u64 gw_hist_get(const u64* p) {
+GW_HD GwU64x2 gw_hist_get(const GwU64x2* p) {
 #if defined(__CUDA_ARCH__)
-    return __ldcs(p);
+    const ulonglong2 v = __ldcs(reinterpret_cast<const ulonglong2*>(p));
+    GwU64x2 r; r.x = v.x; r.y = v.y;
+    return r;
 #else
     return *p;
 #endif
 }
-// 32 rows [lo, lo + 32) of a column given as NB blocks (rows outside [0, 64 * NB) read as 0)
-template <int NB>
-GW_HD uint32_t gw_dp_band(const u64 (&w)[NB], int lo) {
-    if (lo <= -32 || lo >= 64 * NB) return 0u;
-    if (lo < 0) return (uint32_t)(w[0] << (-lo));
-    const int b = lo >> 6, off = lo & 63;
-    u64 x0 = 0ULL, x1 = 0ULL;
-#pragma unroll
-    for (int r = 0; r < NB; ++r) { if (r == b) x0 = w[r]; if (r == b + 1) x1 = w[r]; }
-    return (uint32_t)((x0 >> off) | ((x1 << 1) << (63 - off)));
-}
-// first row of the band kept for window column `col`: 16 rows above the window's main diagonal (a fragment of m rows in a window of
-// ncols columns sits (ncols - m) / 2 columns in)
-GW_HD int gw_dp_band_lo(int m, int ncols, int col) { return col - (ncols - m) / 2 - 16; }
 
 struct GwVerifyOut {
     int valid;   // 0: reference returns null
@@ -62,14 +46,13 @@ struct GwDp {
 
 GW_HD int gw_score_boundary(int m, int band_k, int r) { return gw_max(m - ((r + 1) * 64) + band_k, 0); }
 
-// hist: scratch base for this request; entry e (what the reference's tables hold at index e: the state after window column e - 1) at
-// hist[e * stride]
-GW_HD void gw_dp_begin(GwDp& d, int m, int Ncols, int band_k, u64* hist, size_t stride) {
+// hist: scratch base for this request; element (col, blk) at hist[((col * bMax + blk) * stride)] as GwU64x2 (vp, vn)
+GW_HD void gw_dp_begin(GwDp& d, int m, int Ncols, int band_k, GwU64x2* hist, size_t stride) {
     d.m = m; d.ncols = Ncols; d.bmax = gw_max(1, (m + 63) / 64); d.j = 0;
 #pragma unroll
     for (int r = 0; r < GW_MAX_NB; ++r) { d.D[r] = 0; d.vp[r] = ~0ULL; d.vn[r] = 0ULL; }
     d.D[0] = m;
-    (void)hist; (void)stride;   // entry 0 (VP = ~0, VN = 0) is never read: the traceback starts at column >= 0, i.e. entry >= 1
+    for (int r = 0; r < d.bmax; ++r) gw_hist_put(&hist[(size_t)r * stride], ~0ULL, 0ULL);  // column 0
     d.bceil = gw_max(1, (band_k + 63) / 64);
     if (d.bceil > d.bmax) d.bceil = d.bmax;  // band_k <= 64 in practice; keeps indices in range
     d.has_best = 0; d.best_tail = -1; d.best_diff = 0;
@@ -79,7 +62,7 @@ GW_HD void gw_dp_begin(GwDp& d, int m, int Ncols, int band_k, u64* hist, size_t 
 // NB: compile-time bound of the number of 64-row blocks (ceil(m / 64) <= NB): the loops over blocks are unrolled to NB, so a 100 bp
 // read does not pay for the two blocks only 250 bp reads have
 template <int NB, typename RefSym>
-GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, u64* hist, size_t stride) {
+GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, GwU64x2* hist, size_t stride) {
     const int w = 64;
     const int m = d.m, bMax = d.bmax;
     int bCeil = d.bceil;
@@ -90,12 +73,10 @@ GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_M
     bool hasBest = d.has_best != 0;
     int bestTail = d.best_tail, bestDiff = d.best_diff;
     if (jEnd > d.ncols) jEnd = d.ncols;
-    u64 pp[NB], pn[NB];   // what the tables hold for the previous column (needed again when this column switches a block on)
-#pragma unroll
-    for (int r = 0; r < NB; ++r) { pp[r] = 0ULL; pn[r] = 0ULL; }
     for (int j = d.j; j < jEnd; ++j) {
         const int ch = refsym(j);
         int carry = 0;
+        GwU64x2* col = hist + (size_t)(j + 1) * bMax * stride;
         int computed = bCeil;  // blocks whose column j+1 is written in this step
 #pragma unroll
         for (int r = 0; r < NB; ++r) {
@@ -111,6 +92,7 @@ GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_M
                 if (carry > 0) hp2 |= 1ULL;
                 vp[r] = hn2 | ~(d0 | hp2);
                 vn[r] = d0 & hp2;
+                gw_hist_put(&col[(size_t)r * stride], vp[r], vn[r]);
                 D[r] += hout;
                 carry = hout;
             }
@@ -122,13 +104,8 @@ GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_M
             if (!activated && r == bCeil && r < bMax) {
                 u64 x = ch < 4 ? peq[ch][r] : 0ULL;
                 if (D[r - 1] - carry <= gw_score_boundary(m, band_k, r - 1) && (((x & 1ULL) != 0ULL) | (carry < 0))) {
-                    // vp[r][j] = ~0, vn[r][j] = 0 (the entry of the PREVIOUS column is overwritten: its band is stored again); then one block step
-                    if (j > 0) {
-#pragma unroll
-                        for (int q = 0; q < NB; ++q) if (q == r) { pp[q] = ~0ULL; pn[q] = 0ULL; }
-                        const int plo = gw_dp_band_lo(m, d.ncols, j - 1);
-                        gw_hist_put(&hist[(size_t)j * stride], gw_dp_band<NB>(pp, plo), gw_dp_band<NB>(pn, plo));
-                    }
+                    // vp[r][j] = ~0, vn[r][j] = 0 ; then one block step
+                    gw_hist_put(&hist[((size_t)j * bMax + r) * stride], ~0ULL, 0ULL);
                     u64 vpr = ~0ULL, vnr = 0ULL;
                     if (carry < 0) x |= 1ULL;
                     u64 d0 = (((x & vpr) + vpr) ^ vpr) | x | vnr;
@@ -140,6 +117,7 @@ GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_M
                     if (carry > 0) hp2 |= 1ULL;
                     vp[r] = hn2 | ~(d0 | hp2);
                     vn[r] = d0 & hp2;
+                    gw_hist_put(&col[(size_t)r * stride], vp[r], vn[r]);
                     D[r] = D[r - 1] - carry + hout;
                     bCeil = r + 1;
                     computed = bCeil;
@@ -152,14 +130,11 @@ GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_M
             for (int r = NB - 1; r >= 1; --r)
                 if (bCeil == r + 1 && D[r] > gw_score_boundary(m, band_k, r) + w) bCeil = r;
         }
-        // what the tables hold for this column: the computed blocks; blocks not computed in this step keep the zero initial value of the
-        // Java arrays (a block deactivated just now was computed and keeps its values, as in the reference). Its band goes to the history.
+        // blocks not computed in this step: column j+1 keeps the zero initial value of the Java arrays
+        // (a block deactivated just now was computed and keeps its values, as in the reference)
 #pragma unroll
-        for (int r = 0; r < NB; ++r) { const bool live = r < computed; pp[r] = live ? vp[r] : 0ULL; pn[r] = live ? vn[r] : 0ULL; }
-        {
-            const int lo = gw_dp_band_lo(m, d.ncols, j);
-            gw_hist_put(&hist[(size_t)(j + 1) * stride], gw_dp_band<NB>(pp, lo), gw_dp_band<NB>(pn, lo));
-        }
+        for (int r = 1; r < NB; ++r)
+            if (r >= computed && r < bMax) gw_hist_put(&col[(size_t)r * stride], 0ULL, 0ULL);
         if (bCeil == bMax) {
             int dl = D[0];
 #pragma unroll
@@ -176,70 +151,17 @@ GW_HD void gw_dp_columns_nb(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_M
 // nb_hint: a caller whose lanes run together passes the largest block count among them, so that all of them take the same
 // instantiation (a lane with fewer blocks only skips the guarded parts) instead of running two instantiations one after the other
 template <typename RefSym>
-GW_HD void gw_dp_columns(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, u64* hist, size_t stride, int nb_hint = 0) {
+GW_HD void gw_dp_columns(GwDp& d, int jEnd, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, GwU64x2* hist, size_t stride, int nb_hint = 0) {
     const int nb = d.bmax > nb_hint ? d.bmax : nb_hint;
     if (nb <= 1) gw_dp_columns_nb<1>(d, jEnd, band_k, peq, refsym, hist, stride);
     else if (nb <= 2) gw_dp_columns_nb<2>(d, jEnd, band_k, peq, refsym, hist, stride);
     else gw_dp_columns_nb<GW_MAX_NB>(d, jEnd, band_k, peq, refsym, hist, stride);
 }
 
-// What the reference's VP / VN tables hold for window column `col` at `row`, by replaying the recurrence from column 0 to col + 1 (the
-// column after `col` may switch a block on, which overwrites that block's entry of `col`). Out of line and slow on purpose: only cells
-// that left the band of the history need it.
-template <typename RefSym>
-GW_COLD void gw_dp_replay(int m, int ncols, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, int col, int row, int* vpbit, int* vnbit) {
-    const int w = 64, bMax = gw_max(1, (m + 63) / 64);
-    int D[GW_MAX_NB], bCeil = gw_min(gw_max(1, (band_k + 63) / 64), bMax);
-    u64 vp[GW_MAX_NB], vn[GW_MAX_NB], sp[GW_MAX_NB], sn[GW_MAX_NB];
-    for (int r = 0; r < GW_MAX_NB; ++r) { D[r] = 0; vp[r] = ~0ULL; vn[r] = 0ULL; sp[r] = 0ULL; sn[r] = 0ULL; }
-    D[0] = m;
-    const int j1 = gw_min(col + 2, ncols);
-    for (int j = 0; j < j1; ++j) {
-        const int ch = refsym(j);
-        int carry = 0, computed = bCeil, act = -1;
-        for (int r = 0; r < bCeil; ++r) {
-            u64 x = ch < 4 ? peq[ch][r] : 0ULL;
-            if (carry < 0) x |= 1ULL;
-            const u64 d0 = (((x & vp[r]) + vp[r]) ^ vp[r]) | x | vn[r];
-            const u64 hp = vn[r] | ~(d0 | vp[r]), hn = d0 & vp[r];
-            const int hout = (int)((hp >> 63) & 1ULL) - (int)((hn >> 63) & 1ULL);
-            u64 hp2 = hp << 1, hn2 = hn << 1;
-            if (carry < 0) hn2 |= 1ULL;
-            if (carry > 0) hp2 |= 1ULL;
-            vp[r] = hn2 | ~(d0 | hp2); vn[r] = d0 & hp2;
-            D[r] += hout; carry = hout;
-        }
-        if (bCeil < bMax) {
-            const int r = bCeil;
-            u64 x = ch < 4 ? peq[ch][r] : 0ULL;
-            if (D[r - 1] - carry <= gw_score_boundary(m, band_k, r - 1) && (((x & 1ULL) != 0ULL) | (carry < 0))) {
-                const u64 vpr = ~0ULL, vnr = 0ULL;
-                if (carry < 0) x |= 1ULL;
-                const u64 d0 = (((x & vpr) + vpr) ^ vpr) | x | vnr;
-                const u64 hp = vnr | ~(d0 | vpr), hn = d0 & vpr;
-                const int hout = (int)((hp >> 63) & 1ULL) - (int)((hn >> 63) & 1ULL);
-                u64 hp2 = hp << 1, hn2 = hn << 1;
-                if (carry < 0) hn2 |= 1ULL;
-                if (carry > 0) hp2 |= 1ULL;
-                vp[r] = hn2 | ~(d0 | hp2); vn[r] = d0 & hp2;
-                D[r] = D[r - 1] - carry + hout;
-                bCeil = r + 1; computed = bCeil; act = r;
-            }
-        }
-        if (act < 0) while (bCeil > 1 && D[bCeil - 1] > gw_score_boundary(m, band_k, bCeil - 1) + w) --bCeil;
-        if (j == col) for (int r = 0; r < GW_MAX_NB; ++r) { const bool live = r < computed; sp[r] = live ? vp[r] : 0ULL; sn[r] = live ? vn[r] : 0ULL; }
-        else if (j == col + 1 && act >= 0) { sp[act] = ~0ULL; sn[act] = 0ULL; }
-    }
-    const int b = row >> 6, off = row & 63;
-    *vpbit = b < GW_MAX_NB ? (int)((sp[b] >> off) & 1ULL) : 0;
-    *vnbit = b < GW_MAX_NB ? (int)((sn[b] >> off) & 1ULL) : 0;
-}
-
 // qsym(i): query symbol (0..4) of row i
 template <typename RefSym, typename QSym>
-GW_HD void gw_dp_traceback(const GwDp& d, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, QSym qsym, const u64* hist, size_t stride, uint32_t* cig_out,
-                           GwVerifyOut* out) {
-    const int m = d.m;
+GW_HD void gw_dp_traceback(const GwDp& d, RefSym refsym, QSym qsym, const GwU64x2* hist, size_t stride, uint32_t* cig_out, GwVerifyOut* out) {
+    const int m = d.m, bMax = d.bmax;
     const bool hasBest = d.has_best != 0;
     const int bestTail = d.best_tail;
     out->cig_overflow = false;
@@ -256,26 +178,17 @@ GW_HD void gw_dp_traceback(const GwDp& d, int band_k, const u64 (*peq)[GW_MAX_NB
     };
     int leftMostPos = 0, diff = 0;
     int col = bestTail, row = m - 1;
-    int hcol = -2;
-    u64 v = 0ULL;
+    int hcol = -2, hblk = -1;
+    GwU64x2 v = GwU64x2{0ULL, 0ULL};
     for (;;) {
         int path = 0;
         if (col >= 0 && row >= 0) {
+            const int block = row >> 6, offset = row & 63;
+            if (col != hcol || block != hblk) { v = gw_hist_get(&hist[((size_t)(col + 1) * bMax + block) * stride]); hcol = col; hblk = block; }
             if (refsym(col) == qsym(row)) path = 1;
-            else {
-                int vpb, vnb;
-                const int rel = row - gw_dp_band_lo(m, d.ncols, col);
-                if (rel >= 0 && rel < 32) {
-                    if (col != hcol) { v = gw_hist_get(&hist[(size_t)(col + 1) * stride]); hcol = col; }
-                    vpb = (int)((v >> rel) & 1ULL);
-                    vnb = (int)((v >> (32 + rel)) & 1ULL);
-                } else
-                    gw_dp_replay(m, d.ncols, band_k, peq, refsym, col, row, &vpb, &vnb);
-                if (vpb) path = 3;
-                else if (!vnb) path = 2;
-                else path = 4;
-                diff++;
-            }
+            else if ((v.x >> offset) & 1ULL) { path = 3; diff++; }
+            else if (!((v.y >> offset) & 1ULL)) { path = 2; diff++; }
+            else { path = 4; diff++; }
         }
         if (path == 1 || path == 2) { push(0); leftMostPos = col; col--; row--; }
         else if (path == 3) { push(1); leftMostPos = col + 1; row--; }
@@ -321,9 +234,9 @@ GW_HD void gw_dp_traceback(const GwDp& d, int band_k, const u64 (*peq)[GW_MAX_NB
 
 template <typename RefSym, typename QSym>
 GW_HD void gw_verify(int m, int Ncols, int band_k, const u64 (*peq)[GW_MAX_NB], RefSym refsym, QSym qsym,
-                                          u64* hist, size_t stride, uint32_t* cig_out, GwVerifyOut* out) {
+                                          GwU64x2* hist, size_t stride, uint32_t* cig_out, GwVerifyOut* out) {
     GwDp d;
     gw_dp_begin(d, m, Ncols, band_k, hist, stride);
     gw_dp_columns(d, Ncols, band_k, peq, refsym, hist, stride);
-    gw_dp_traceback(d, band_k, peq, refsym, qsym, hist, stride, cig_out, out);
+    gw_dp_traceback(d, refsym, qsym, hist, stride, cig_out, out);
 }

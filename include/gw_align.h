@@ -172,20 +172,22 @@ int gw_verify_pairs(int device, const char* refs, const uint64_t* ref_off, const
  * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). Same computation and same outputs as gw_verify_pairs, but
  *  - every pointer is a DEVICE pointer on `device` (refs/queries: ACGTN characters; *_off: n + 1 ascending byte offsets; d_result: n x 4
  *    int32; d_cigar_ops: n x cigar_stride uint32, rows are zero-filled after the cigar as gw_verify_pairs leaves them);
- *  - the DP history (the verifier's only scratch memory, 8 bytes per pair and reference column) lives in a static device array of
+ *  - the DP history (the verifier's only scratch memory, 16 bytes per pair, reference column and 64-base block of the query) lives in a
+ *    static device array of
  *    GW_VERIFY_PAIRS_NOALLOC_MAX_BYTES that every GPU which loads the library holds until the process exits. The call allocates and frees
  *    nothing (no cudaMalloc / cudaFree, no allocating library routine) and is ASYNCHRONOUS on `stream` (a cudaStream_t, NULL = default
  *    stream): synchronise the stream before reading the outputs;
- *  - max_ref_len: an upper bound of the reference (window) lengths of the batch, stated by the caller because the offsets are on the device.
- *    n * (max_ref_len + 2) * 8 bytes must fit the static array, else GW_E_ARG with a message that says so; a pair whose reference is longer
- *    than max_ref_len (or whose query exceeds 256 bases) gets result[i*4] = GW_NOALLOC_PAIR_TOO_LONG and is not aligned.
+ *  - max_ref_len / max_query_len: upper bounds of the reference (window) and query lengths of the batch, stated by the caller because the
+ *    offsets are on the device. n * (max_ref_len + 2) * ceil(max_query_len / 64) * 16 bytes must fit the static array (about 19 400 pairs of
+ *    100-base queries with 106-base windows), else GW_E_ARG with a message that says so; a pair longer than stated gets
+ *    result[i*4] = GW_NOALLOC_PAIR_TOO_LONG and is not aligned.
  * All calls share the one array per GPU, which keeps the last call's contents (nothing in it has to start at zero: every word read was
  * written by the same launch). Two calls whose kernels overlap on one GPU (different streams or host threads) RACE on it: serialise them. */
-#define GW_VERIFY_PAIRS_NOALLOC_MAX_BYTES (32u << 20)
+#define GW_VERIFY_PAIRS_NOALLOC_MAX_BYTES (64u << 20)
 #define GW_NOALLOC_PAIR_TOO_LONG (-2)
 int gw_verify_pairs_noalloc(int device, void* stream, const char* d_refs, const uint64_t* d_ref_off, const char* d_queries,
-                            const uint64_t* d_query_off, uint32_t n, uint32_t max_ref_len, int band_k, int32_t* d_result, uint32_t* d_cigar_ops,
-                            uint32_t cigar_stride);
+                            const uint64_t* d_query_off, uint32_t n, uint32_t max_ref_len, uint32_t max_query_len, int band_k, int32_t* d_result,
+                            uint32_t* d_cigar_ops, uint32_t cigar_stride);
 /* StaircaseFilter(m, kk) masks (align/strategy/StaircaseFilter.java:47-73): (kk+1) x ceil(m/64) words; returns 2 if the reference throws
  * (never with extended != 0: gw_config_t.extended) */
 int gw_staircase_table(int m, int kk, int extended, uint64_t* out, int cap_words);

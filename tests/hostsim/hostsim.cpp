@@ -105,7 +105,7 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
         std::vector<u64*> slabs(n_reads, nullptr);
         uint32_t max_m = 1;
         for (uint32_t i = 0; i < n_reads; ++i) max_m = std::max<uint32_t>(max_m, (uint32_t)std::min<uint64_t>(offsets[i + 1] - offsets[i], GW_MAX_READ_LEN));
-        std::vector<u64> hist((size_t)(max_m + 2 * kmax + 2), 0xDEADBEEFDEADBEEFULL);   // poison
+        std::vector<GwU64x2> hist((size_t)(max_m + 2 * kmax + 2) * ((max_m + 63) / 64), GwU64x2{0xDEADBEEFDEADBEEFULL, 0xFEEDFACEFEEDFACEULL});   // poison
         // GWSIM_NOCACHE=1: the lane re-reads its state from the work area before every slice; GWSIM_SPILL=n: the lane is written back
         // and re-read every n slices (as the flow kernel does around its out-of-line continuations). Neither may change any result.
         const bool nocache = getenv("GWSIM_NOCACHE") && atoi(getenv("GWSIM_NOCACHE"));
@@ -224,7 +224,7 @@ int gwsim_verify_pair(const char* ref, const char* query, int band_k, int* pos, 
         if (c == 4) { for (int a = 0; a < 4; ++a) peq[a][j >> 6] |= 1ULL << (j & 63); }
         else peq[c][j >> 6] |= 1ULL << (j & 63);
     }
-    std::vector<u64> hist((size_t)(Ncols + 2), 0xDEADBEEFDEADBEEFULL);   // poison: device scratch is not zeroed
+    std::vector<GwU64x2> hist((size_t)(Ncols + 2) * std::max(1, (m + 63) / 64), GwU64x2{0xDEADBEEFDEADBEEFULL, 0xFEEDFACEFEEDFACEULL});   // poison: device scratch is not zeroed
     GwVerifyOut out;
     gw_verify(m, Ncols, band_k, peq, refsym, qsym, hist.data(), 1, cig, &out);
     *pos = out.pos; *nm = out.diff; *cig_n = out.cig_n;

@@ -10,7 +10,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 STRIDE = 40
-MAX_BYTES = 32 << 20   # GW_VERIFY_PAIRS_NOALLOC_MAX_BYTES
+MAX_BYTES = 64 << 20   # GW_VERIFY_PAIRS_NOALLOC_MAX_BYTES
 
 
 def _pairs(n, seed, lengths):
@@ -61,9 +61,9 @@ def _noalloc(L, torch, pairs, k, bufs):
     d_res.fill_(-7)       # outputs start as garbage: the entry point must write every word it owns
     d_cig.fill_(-1)
     torch.cuda.synchronize()
-    max_ref = max(len(r) for r, _ in pairs)
+    max_ref, max_q = max(len(r) for r, _ in pairs), max(len(q) for _, q in pairs)
     free_before = torch.cuda.mem_get_info()[0]
-    rc = L.lib().gw_verify_pairs_noalloc(0, None, d_refs.data_ptr(), d_ro.data_ptr(), d_qs.data_ptr(), d_qo.data_ptr(), n, max_ref, k,
+    rc = L.lib().gw_verify_pairs_noalloc(0, None, d_refs.data_ptr(), d_ro.data_ptr(), d_qs.data_ptr(), d_qo.data_ptr(), n, max_ref, max_q, k,
                                          d_res.data_ptr(), d_cig.data_ptr(), STRIDE)
     L.check(rc)
     torch.cuda.synchronize()
@@ -83,14 +83,14 @@ def test_no_alloc_verifier_matches_the_existing_entry_point_twice():
     bufs = (torch.empty(cap_bytes, dtype=torch.uint8, device=dev), torch.empty(cap_n + 1, dtype=torch.int64, device=dev),
             torch.empty(cap_bytes, dtype=torch.uint8, device=dev), torch.empty(cap_n + 1, dtype=torch.int64, device=dev),
             torch.empty(cap_n * 4, dtype=torch.int32, device=dev), torch.empty(cap_n * STRIDE, dtype=torch.int32, device=dev))
-    # call 1: 6000 pairs of mixed lengths (1 to 4 DP blocks); call 2: other, fewer and shorter pairs over the scratch call 1 left behind;
+    # call 1: 3000 pairs of mixed lengths (1 to 4 DP blocks); call 2: other, fewer and shorter pairs over the scratch call 1 left behind;
     # call 3: call 1's pairs again
-    first = _pairs(6000, 101, [36, 64, 65, 100, 128, 150, 200, 250])
-    second = _pairs(2500, 202, [50, 100, 75])
+    first = _pairs(3000, 101, [36, 64, 65, 100, 128, 150, 200, 250])
+    second = _pairs(2000, 202, [50, 100, 75])
     for call, (pairs, k) in enumerate(((first, 6), (second, 3), (first, 6))):
         want_res, want_cig = _existing(L, pairs, k)
         got_res, got_cig, grew = _noalloc(L, torch, pairs, k, bufs)
-        # the first use in a process may load the CUDA module that holds the static array (that is when the GPU commits its 32 MiB);
+        # the first use in a process may load the CUDA module that holds the static array (that is when the GPU commits its 64 MiB);
         # from then on the memory in use on the device must not move across a call
         assert call == 0 or grew <= 0, "device memory in use grew by %d bytes across call %d" % (grew, call)
         assert np.array_equal(got_res, want_res)
@@ -103,8 +103,8 @@ def test_no_alloc_verifier_rejects_what_the_scratch_cannot_hold():
     from genome_weaver_align_b200 import _lib as L
     torch.cuda.set_device(0)
     z = torch.zeros(16, dtype=torch.int64, device="cuda:0")
-    n = MAX_BYTES // ((106 + 2) * 8) + 1    # one pair more than the static array holds at 106 reference columns
-    rc = L.lib().gw_verify_pairs_noalloc(0, None, z.data_ptr(), z.data_ptr(), z.data_ptr(), z.data_ptr(), n, 106, 3, z.data_ptr(), z.data_ptr(), STRIDE)
+    n = MAX_BYTES // ((106 + 2) * 2 * 16) + 1    # one pair more than the static array holds at 106 reference columns and 100-base queries
+    rc = L.lib().gw_verify_pairs_noalloc(0, None, z.data_ptr(), z.data_ptr(), z.data_ptr(), z.data_ptr(), n, 106, 100, 3, z.data_ptr(), z.data_ptr(), STRIDE)
     assert rc == -1   # GW_E_ARG, nothing launched
     with pytest.raises(L.GwError, match="static scratch"):
         L.check(rc)
@@ -116,7 +116,7 @@ def test_no_alloc_verifier_rejects_what_the_scratch_cannot_hold():
     o = [torch.from_numpy(np.asarray(a, dtype=np.uint64).view(np.int64).copy()).cuda() for a in (ro, qo)]
     res = torch.full((8,), -7, dtype=torch.int32, device="cuda:0")
     cig = torch.full((2 * STRIDE,), -1, dtype=torch.int32, device="cuda:0")
-    L.check(L.lib().gw_verify_pairs_noalloc(0, None, d[0].data_ptr(), o[0].data_ptr(), d[1].data_ptr(), o[1].data_ptr(), 2, 20, 3, res.data_ptr(),
+    L.check(L.lib().gw_verify_pairs_noalloc(0, None, d[0].data_ptr(), o[0].data_ptr(), d[1].data_ptr(), o[1].data_ptr(), 2, 20, 10, 3, res.data_ptr(),
                                             cig.data_ptr(), STRIDE))
     torch.cuda.synchronize()
     r = res.cpu().numpy().reshape(2, 4)
