@@ -322,6 +322,75 @@ __global__ void gw_collect_overflow_kernel(u64* const* slabs, uint32_t n, uint32
     if (c->status == GW_ST_OVERFLOW) list[atomicAdd(count, 1u)] = i;
 }
 
+// ---- work order of a wave ---------------------------------------------------------------------------------
+// The flow kernel hands reads to its warps 32 at a time in the order of the work list. Ordered by the quick scan's verdict — the reads
+// with the most mismatching stretches first, reads with an exact hit last — the 32 reads a warp takes up need about the same amount of
+// search (its lanes stay in step), and the kernel ends on the cheapest reads instead of waiting for a few expensive ones. The order
+// changes no result: reads are independent and every output is addressed by read. Stable counting sort over GW_ORDER_CLASSES classes:
+// per-CTA class counts, one scan over (class, CTA), stable scatter.
+#define GW_ORDER_CLASSES 8
+#define GW_ORDER_T 256
+GW_HD int gw_order_class(const GwReadCtx* c) {
+    if (c->phase == GW_PH_DONE) return 7;                       // nothing to do (empty / unsupported read)
+    const int mm = gw_min(c->scan_mm[0], c->scan_mm[1]);
+    if (mm == 0) return 6;                                      // exact hit: one locate
+    if (mm > c->k) return 5;                                    // neither strand can be within k: finishes when taken up
+    return mm >= 5 ? 0 : 5 - mm;                                // searched: more mismatching stretches = more states
+}
+// ranks of the CTA's reads within their class (stable): warp part by match_any, CTA part by a table of per-warp counts
+__device__ __forceinline__ uint32_t gw_order_rank(int cls, bool valid, uint32_t (*wcnt)[GW_ORDER_CLASSES], uint32_t* cta_total_of_class) {
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint32_t same = __match_any_sync(0xFFFFFFFFu, valid ? cls : GW_ORDER_CLASSES);
+    const uint32_t in_warp = (uint32_t)__popc(same & ((1u << lane) - 1u));
+    if (threadIdx.x < (GW_ORDER_T / 32) * GW_ORDER_CLASSES) wcnt[threadIdx.x / GW_ORDER_CLASSES][threadIdx.x % GW_ORDER_CLASSES] = 0;
+    __syncthreads();
+    if (valid && in_warp == 0) wcnt[wid][cls] = (uint32_t)__popc(same);
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+    if (valid) {
+        for (uint32_t w = 0; w < GW_ORDER_T / 32; ++w) { const uint32_t v = wcnt[w][cls]; if (w < wid) before += v; total += v; }
+    }
+    *cta_total_of_class = total;
+    return before + in_warp;
+}
+__global__ void __launch_bounds__(GW_ORDER_T) gw_order_count_kernel(u64* const* slabs, uint32_t n, uint8_t* cls_out, uint32_t* counts /* [class][CTA] */) {
+    __shared__ uint32_t wcnt[GW_ORDER_T / 32][GW_ORDER_CLASSES];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = i < n;
+    const int cls = valid ? gw_order_class(reinterpret_cast<const GwReadCtx*>(slabs[i])) : 0;
+    if (valid) cls_out[i] = (uint8_t)cls;
+    uint32_t total = 0;
+    const uint32_t rank = gw_order_rank(cls, valid, wcnt, &total);
+    if (valid && rank == 0) counts[(size_t)cls * gridDim.x + blockIdx.x] = total;
+}
+// exclusive scan of `len` counts in place (one CTA; len = classes x CTAs, tens of thousands at most)
+__global__ void __launch_bounds__(1024) gw_order_scan_kernel(uint32_t* counts, uint32_t len) {
+    __shared__ uint32_t sh[1024];
+    const uint32_t t = threadIdx.x, chunk = (len + 1023u) / 1024u;
+    const uint32_t lo = min(len, t * chunk), hi = min(len, lo + chunk);
+    uint32_t sum = 0;
+    for (uint32_t i = lo; i < hi; ++i) sum += counts[i];
+    sh[t] = sum;
+    __syncthreads();
+    for (uint32_t d = 1; d < 1024; d <<= 1) {
+        const uint32_t y = t >= d ? sh[t - d] : 0;
+        __syncthreads();
+        sh[t] += y;
+        __syncthreads();
+    }
+    uint32_t run = sh[t] - sum;
+    for (uint32_t i = lo; i < hi; ++i) { const uint32_t v = counts[i]; counts[i] = run; run += v; }
+}
+__global__ void __launch_bounds__(GW_ORDER_T) gw_order_scatter_kernel(const uint8_t* cls_in, uint32_t n, const uint32_t* offsets /* [class][CTA] */, uint32_t* order) {
+    __shared__ uint32_t wcnt[GW_ORDER_T / 32][GW_ORDER_CLASSES];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = i < n;
+    const int cls = valid ? (int)cls_in[i] : 0;
+    uint32_t total = 0;
+    const uint32_t rank = gw_order_rank(cls, valid, wcnt, &total);
+    if (valid) order[offsets[(size_t)cls * gridDim.x + blockIdx.x] + rank] = i;
+}
+
 __global__ void gw_settle_kernel(u64** slabs, u64* small_base, size_t small_words, GwSlabParams small_sp, const uint32_t* list, uint32_t n, GwDevConfig cfg) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -520,6 +589,16 @@ void gwk_densify(cudaStream_t st, const GwIndexView& ix, int fm, uint32_t step, 
 }
 void gwk_collect_overflow(cudaStream_t st, u64* const* slabs, uint32_t n, uint32_t* list, uint32_t* count) {
     if (n) gw_collect_overflow_kernel<<<gw_grid(n, 256), 256, 0, st>>>(slabs, n, list, count);
+}
+// order[0..n) = the slots 0..n-1 sorted by gw_order_class (stable); cls: n bytes, counts: GW_ORDER_CLASSES x ceil(n / 256) words of scratch
+size_t gwk_order_scratch_words(uint32_t n) { return (size_t)GW_ORDER_CLASSES * gw_grid(n, GW_ORDER_T); }
+void gwk_order(cudaStream_t st, u64* const* slabs, uint32_t n, uint8_t* cls, uint32_t* counts, uint32_t* order) {
+    if (!n) return;
+    const unsigned blocks = gw_grid(n, GW_ORDER_T);
+    cudaMemsetAsync(counts, 0, (size_t)GW_ORDER_CLASSES * blocks * 4, st);
+    gw_order_count_kernel<<<blocks, GW_ORDER_T, 0, st>>>(slabs, n, cls, counts);
+    gw_order_scan_kernel<<<1, 1024, 0, st>>>(counts, GW_ORDER_CLASSES * blocks);
+    gw_order_scatter_kernel<<<blocks, GW_ORDER_T, 0, st>>>(cls, n, counts, order);
 }
 void gwk_settle(cudaStream_t st, u64** slabs, u64* small_base, size_t small_words, const GwSlabParams& small_sp, const uint32_t* list, uint32_t n, const GwDevConfig& cfg) {
     if (n) gw_settle_kernel<<<gw_grid(n, 128), 128, 0, st>>>(slabs, small_base, small_words, small_sp, list, n, cfg);

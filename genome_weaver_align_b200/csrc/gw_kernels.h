@@ -24,6 +24,8 @@ void gwk_gather_bench(cudaStream_t st, const GwIndexView& ix, int which, uint32_
 void gwk_rank_acgtn(cudaStream_t st, const GwIndexView& ix, int which, const uint32_t* pos, uint32_t n, uint32_t* out);
 void gwk_locate_rows(cudaStream_t st, const GwIndexView& ix, int which, const uint32_t* rows, uint32_t n, uint32_t* out);
 void gwk_scan_export(cudaStream_t st, u64* const* slabs, uint32_t n, int strand, uint32_t* out);
+size_t gwk_order_scratch_words(uint32_t n);
+void gwk_order(cudaStream_t st, u64* const* slabs, uint32_t n, uint8_t* cls, uint32_t* counts, uint32_t* order);
 void gwk_verify_pairs(cudaStream_t st, const char* refs, const u64* ref_off, const char* queries, const u64* query_off, uint32_t n, int band_k,
                       int32_t* result, uint32_t* cigar_ops, uint32_t cigar_stride, void* hist, uint32_t max_m);
 // gw_noalloc.cu: the pair verifier with its DP history in a static __device__ array (no allocation anywhere on the call path)

@@ -238,7 +238,8 @@ def test_sam_parity_moves_to_larger_work_areas(small, opts):
 
 
 @pytest.mark.parametrize("opts", [dict(flow_batch=1, flow_age=1), dict(flow_batch=32, flow_age=1000, flow_flush=32),
-                                  dict(flow_fetch=1, flow_flush=1, flow_blocks=3), dict(flow_blocks=1), dict(flow_blocks=1000)])
+                                  dict(flow_fetch=1, flow_flush=1, flow_blocks=3), dict(flow_blocks=1), dict(flow_blocks=1000),
+                                  dict(flow_order=0), dict(flow_order=1, flow_blocks=7)])
 def test_sam_parity_flow_kernel_tunables(small, opts):
     # how the warps of the flow kernel batch their work (deferred continuations, verification batches, grid size) must not change
     # any result
