@@ -328,14 +328,18 @@ __global__ void gw_collect_overflow_kernel(u64* const* slabs, uint32_t n, uint32
 // search (its lanes stay in step), and the kernel ends on the cheapest reads instead of waiting for a few expensive ones. The order
 // changes no result: reads are independent and every output is addressed by read. Stable counting sort over GW_ORDER_CLASSES classes:
 // per-CTA class counts, one scan over (class, CTA), stable scatter.
-#define GW_ORDER_CLASSES 8
+#define GW_ORDER_CLASSES 32
 #define GW_ORDER_T 256
+// Measured on the bench configs (tools/order_study.py): a searched read costs about one FM search per base whatever its mismatch count
+// (98 / 101 / 111 searches for 1 / 2 / 3 mismatching stretches at 100 bp), so the length decides, then the mismatches; a read with an
+// exact hit costs one locate. Classes: 8 length groups of 32 bases (longest first) x 3 mismatch groups, then the reads that need no search.
 GW_HD int gw_order_class(const GwReadCtx* c) {
-    if (c->phase == GW_PH_DONE) return 7;                       // nothing to do (empty / unsupported read)
+    if (c->phase == GW_PH_DONE) return 31;                      // nothing to do (empty / unsupported read)
     const int mm = gw_min(c->scan_mm[0], c->scan_mm[1]);
-    if (mm == 0) return 6;                                      // exact hit: one locate
-    if (mm > c->k) return 5;                                    // neither strand can be within k: finishes when taken up
-    return mm >= 5 ? 0 : 5 - mm;                                // searched: more mismatching stretches = more states
+    if (mm == 0) return 30;                                     // exact hit: one locate
+    if (mm > c->k) return 29;                                   // neither strand can be within k: finishes when taken up
+    const int len = 7 - gw_min(7, (c->m - 1) >> 5);             // 0: 225..256 bases ... 7: 1..32
+    return len * 3 + (mm >= 3 ? 0 : 3 - mm);
 }
 // ranks of the CTA's reads within their class (stable): warp part by match_any, CTA part by a table of per-warp counts
 __device__ __forceinline__ uint32_t gw_order_rank(int cls, bool valid, uint32_t (*wcnt)[GW_ORDER_CLASSES], uint32_t* cta_total_of_class) {
