@@ -68,7 +68,10 @@ struct DBuf {
     size_t cap = 0;
     void ensure(size_t bytes, bool keep = false, cudaStream_t st = 0) {
         if (bytes <= cap) return;
-        size_t ncap = std::max(bytes, cap + cap / 2);
+        // large buffers are sized from a memory budget (align_device): they grow to exactly what is asked for, and the old block is
+        // given back first when its contents are not needed
+        size_t ncap = bytes >= ((size_t)1 << 30) ? bytes : std::max(bytes, cap + cap / 2);
+        if (!keep && p) { cudaFree(p); p = nullptr; cap = 0; }
         void* np = nullptr;
         CK(cudaMalloc(&np, ncap));
         if (keep && p && cap) { CK(cudaMemcpyAsync(np, p, cap, cudaMemcpyDeviceToDevice, st)); CK(cudaStreamSynchronize(st)); }

@@ -32,8 +32,8 @@ GW_HD void gw_prep_read(const GwBatchView& bv, u64* slab_base, const GwSlabParam
     GwReadCtx* c = s.ctx();
     const u64 b0 = bv.offsets[read_id], b1 = bv.offsets[read_id + 1];
     const long long len = (long long)(b1 - b0);
-    c->sp = sp;
-    c->ext = nullptr; c->ext_pool = bv.ext_pool;
+    s.layout_init();
+    c->ext_pool = bv.ext_pool;
     c->read_id = (int32_t)read_id;
     c->m = (int32_t)(len > 0x7fffffffLL ? 0x7fffffff : len);
     c->k = 0;
@@ -194,8 +194,8 @@ GW_HD void gw_settle(u64* big_base, u64* small_base, const GwSlabParams& small_s
     GwSlab sm(small_base, small_sp);
     GwReadCtx* sc = sm.ctx();
     for (uint32_t i = 0; i < GW_CTX_WORDS; ++i) small_base[i] = big_base[i];
-    sc->sp = small_sp;
-    sc->ext = nullptr; sc->ext_pool = nullptr;
+    sm.layout_init();
+    sc->ext_pool = nullptr;
     sc->qn = 0; sc->free1 = -1;
     sc->top = (int32_t)sm.arena_begin();
     const int nrep = gw_num_reported(bc, cfg);

@@ -94,17 +94,27 @@ struct GwSlabParams {
     uint32_t slab_words;   // size of one read slab in 8-byte words
     uint32_t queue_cap;    // max live states in the priority queue
     uint32_t hit_cap;      // max entries of the hit list
+    uint32_t queue_at;     // word offset of the priority queue in the work area; 0 in parameters made on the host = the standard place
+                           // (GW_QUEUE_BASE, gw_state.cuh). A read that moves into a larger block takes its queue to the end of the
+                           // block, with a larger capacity (gw_promote_commit); slab_words is then where the arena ends.
 };
 
 // pool of larger work areas (device memory): a read whose work area is nearly full is moved into ONE block of the pool between two
 // search steps and goes on there, instead of being run again from the start. `next` is the allocation cursor (atomic, reset by
 // the host for every wave).
+// blocks a running read can move its work area into when the arena is nearly full (gw_promote_*): two sizes; a read moves from its
+// first work area into a block of the first size and, if that fills up too, from there into one of the second size
 struct GwExtPool {
     u64* base;
     uint32_t n_blocks;
     uint32_t block_words;
     uint32_t next;
     uint32_t pad_;
+    u64* base2;            // second size (block_words2 > block_words), or n_blocks2 == 0
+    uint32_t n_blocks2;
+    uint32_t block_words2;
+    uint32_t next2;
+    uint32_t pad2_;
 };
 
 // staircase filter tables for every read length present in a batch

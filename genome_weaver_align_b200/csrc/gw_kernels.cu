@@ -213,7 +213,7 @@ __global__ void __launch_bounds__(GW_FLOW_THREADS, 2) gw_flow_kernel(GwSearchEnv
         // ---- one search slice per lane
         int r = GW_STEP_CONTINUE;
         {   // work areas that are nearly full: the reads go on in a larger one; the lanes of the warp share each copy
-            const bool wantp = have && ln.mid == 0 && gw_wants_promotion(s, (uint32_t)ln.top, ln.k);
+            const bool wantp = have && ln.mid == 0 && gw_wants_promotion(s, (uint32_t)ln.top, ln.k, ln.qn);
             if (__ballot_sync(FULL, wantp) != 0u) {
                 if (wantp) gw_lane_flush(s, ln);   // the copy takes the work area as it is in HBM
                 u64* nb = wantp ? gw_promote_take(s) : nullptr;

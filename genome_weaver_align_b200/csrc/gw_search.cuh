@@ -411,7 +411,17 @@ GW_HD bool gw_add_result(const GwSlab& s, const GwDevConfig& cfg, int32_t hit) {
         const GwHitNode* e = gw_hit(s, hl[i]);
         if (gw_hit_total_diff(s, e) <= c->min_mm && gw_hit_total_match(s, e) >= c->max_match_len) hl[w++] = hl[i];
     }
-    if ((uint32_t)w >= s.sp.hit_cap) return false;
+    if ((uint32_t)w >= c->sp.hit_cap) {
+        // the hit list is full (ALLHITS on repeats): it moves into the arena with twice the capacity — the arena is what grows when a
+        // read moves to a larger work area — and the old list is abandoned. The context holds the place and the capacity (s.sp is a copy).
+        const uint32_t ncap = c->sp.hit_cap * 2u;
+        const int32_t at = gw_alloc(s, (ncap + 1u) / 2u);
+        if (at < 0) return false;
+        int32_t* nl = reinterpret_cast<int32_t*>(s.at(at));
+        for (int i = 0; i < w; ++i) nl[i] = hl[i];
+        c->hits_at = (uint32_t)at; c->sp.hit_cap = ncap;
+        hl = nl;
+    }
     hl[w++] = hit;
     c->n_hits = w;
     return true;

@@ -36,7 +36,8 @@ struct GwJob {
 };
 
 struct GwReadCtx {
-    u64* ext;              // the larger block this read was moved to while running (gw_promote), or null
+    uint32_t area_words;   // size of the work area the read lives in (sp.slab_words is where its arena ends)
+    uint32_t hits_at;      // word offset of the hit list (it stays where gw_layout_init put it)
     GwExtPool* ext_pool;   // pool of such blocks, or null
     int32_t m, k;
     int32_t min_mm, max_match_len, best_score;
@@ -69,12 +70,18 @@ struct GwSlab {
     GwSlabParams sp;
     GW_HD GwSlab() : base(nullptr) {}
     GW_HD explicit GwSlab(u64* b) : base(b) { sp = reinterpret_cast<GwReadCtx*>(b)->sp; }
-    GW_HD GwSlab(u64* b, const GwSlabParams& p) : base(b), sp(p) {}
+    GW_HD GwSlab(u64* b, const GwSlabParams& p) : base(b), sp(p) { if (sp.queue_at == 0u) sp.queue_at = GW_QUEUE_BASE; }
     GW_HD GwReadCtx* ctx() const { return reinterpret_cast<GwReadCtx*>(base); }
     // priority queue: one 16-byte entry per queued state — the sort key (comparator of StateQueue packed into one integer, cached at
     // insertion) next to the state offset, so that a sift step is ONE 128-bit load per level
-    GW_HD GwQEntry* queue() const { return reinterpret_cast<GwQEntry*>(base + GW_QUEUE_BASE); }
-    GW_HD int32_t* hits() const { return reinterpret_cast<int32_t*>(base + GW_QUEUE_BASE + 2u * sp.queue_cap); }
+    GW_HD GwQEntry* queue() const { return reinterpret_cast<GwQEntry*>(base + sp.queue_at); }
+    GW_HD int32_t* hits() const { return reinterpret_cast<int32_t*>(base + ctx()->hits_at); }   // cold paths only
+    // a fresh work area with the standard layout: context, queue, hit list, arena
+    GW_HD void layout_init() {
+        sp.queue_at = GW_QUEUE_BASE;
+        GwReadCtx* c = ctx();
+        c->sp = sp; c->area_words = sp.slab_words; c->hits_at = GW_QUEUE_BASE + 2u * sp.queue_cap;
+    }
     // 128-byte aligned: a state of a read with k <= 3 (16 words) is exactly one line
     GW_HD uint32_t arena_begin() const { return (GW_QUEUE_BASE + 2u * sp.queue_cap + (sp.hit_cap + 1) / 2 + 15u) & ~15u; }
     GW_HD u64* at(int32_t off) const { return base + off; }
@@ -179,19 +186,27 @@ GW_HD uint32_t gw_step_alloc_bound(int k) {
     return 9u * gw_state_words(k) + 2u * ((GW_HIT_WORDS + GW_CIG_CAP / 2u + 1u) & ~1u);
 }
 // `top`: the read's allocation cursor (kept in a register by the search lanes)
-GW_HD bool gw_wants_promotion(const GwSlab& s, uint32_t top, int k) {
-    if (top + gw_step_alloc_bound(k) <= s.sp.slab_words) return false;
-    const GwReadCtx* c = s.ctx();
-    return c->ext_pool != nullptr && c->ext == nullptr;
+#define GW_STEP_QUEUE_BOUND 8u   // queue entries one search slice can add (candidate, split and soft-clip children), generously
+GW_HD bool gw_wants_promotion(const GwSlab& s, uint32_t top, int k, int qn) {
+    if (top + gw_step_alloc_bound(k) <= s.sp.slab_words && (uint32_t)qn + GW_STEP_QUEUE_BOUND <= s.sp.queue_cap) return false;
+    return s.ctx()->ext_pool != nullptr;   // cleared when the pool has nothing larger left for this read (gw_promote_take)
 }
 // the move in three parts, so that the copy can be shared by the lanes of a warp: take a block from the pool (null: none left) ...
 GW_COLD u64* gw_promote_take(const GwSlab& s) {
     GwReadCtx* c = s.ctx();
     GwExtPool* pool = c->ext_pool;
-    if (pool->block_words <= s.sp.slab_words) { c->ext_pool = nullptr; return nullptr; }   // already in a work area of that size
-    const uint32_t idx = gw_atomic_add(&pool->next, 1u);
-    if (idx >= pool->n_blocks) { c->ext_pool = nullptr; return nullptr; }
-    return pool->base + (size_t)idx * pool->block_words;
+    const uint32_t cur = c->area_words;
+    if (pool->block_words > cur && pool->next < pool->n_blocks) {
+        const uint32_t idx = gw_atomic_add(&pool->next, 1u);
+        if (idx < pool->n_blocks) return pool->base + (size_t)idx * pool->block_words;
+    }
+    // the second size: for reads that filled a block of the first, and for those that found none left
+    if (pool->n_blocks2 != 0u && pool->block_words2 > cur && pool->next2 < pool->n_blocks2) {
+        const uint32_t idx = gw_atomic_add(&pool->next2, 1u);
+        if (idx < pool->n_blocks2) return pool->base2 + (size_t)idx * pool->block_words2;
+    }
+    c->ext_pool = nullptr;   // nothing larger for this read: it runs until its work area is full and is run again in a later pass
+    return nullptr;
 }
 // ... copy the used part of the work area [0, top) (top is even: the arena starts at an even word, nodes are multiples of two
 // words), `part` of `parts` ...
@@ -200,15 +215,25 @@ GW_HD void gw_promote_copy(const u64* from, u64* to, uint32_t top, uint32_t part
     GwU64x2* dst = reinterpret_cast<GwU64x2*>(to);
     for (uint32_t i = part; i < top / 2u; i += parts) dst[i] = src[i];
 }
-// ... and make the block the read's work area
+// ... and make the block the read's work area: the queue goes to the end of the block with the capacity a work area of that size has
+// (its entries are state offsets, which do not change: the arena stays where it is and now ends where the queue begins)
 GW_HD void gw_promote_commit(GwSlab& s, u64* nb, u64** slab_ptr) {
     GwReadCtx* nc = reinterpret_cast<GwReadCtx*>(nb);
-    const uint32_t words = nc->ext_pool->block_words;
-    nc->sp.slab_words = words;
-    nc->ext = nb;   // marks the read as moved (it is not moved twice)
+    const GwExtPool* pool = nc->ext_pool;
+    const bool second = pool->n_blocks2 != 0u && nb >= pool->base2 && nb < pool->base2 + (size_t)pool->n_blocks2 * pool->block_words2;
+    const uint32_t words = second ? pool->block_words2 : pool->block_words;
+    uint32_t ncap = words / 16u;
+    if (ncap > 8192u) ncap = 8192u;
+    if (ncap < s.sp.queue_cap) ncap = s.sp.queue_cap;
+    const uint32_t nat = words - 2u * ncap;
+    const GwQEntry* from = s.queue();   // in the work area the read leaves (at its end if that was a block already: not part of the copy)
+    GwQEntry* to = reinterpret_cast<GwQEntry*>(nb + nat);
+    for (int32_t i = 0; i < nc->qn; ++i) to[i] = from[i];
+    nc->sp.queue_at = nat; nc->sp.queue_cap = ncap; nc->sp.slab_words = nat;
+    nc->area_words = words;
     *slab_ptr = nb;
     s.base = nb;
-    s.sp.slab_words = words;
+    s.sp = nc->sp;
 }
 GW_COLD bool gw_promote(GwSlab& s, u64** slab_ptr) {
     u64* nb = gw_promote_take(s);

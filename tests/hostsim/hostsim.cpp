@@ -32,6 +32,7 @@ GwSlabParams slab_params(uint32_t words) {   // same rule as gw_api_align.inc
     sp.slab_words = words;
     sp.queue_cap = std::max<uint32_t>(64, std::min<uint32_t>(words / 16, 8192));
     sp.hit_cap = std::max<uint32_t>(32, std::min<uint32_t>(words / 64, 2048));
+    sp.queue_at = 0;
     return sp;
 }
 }  // namespace
@@ -108,6 +109,22 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
         std::vector<GwU64x2> hist((size_t)(max_m + 2 * kmax + 2) * ((max_m + 63) / 64), GwU64x2{0xDEADBEEFDEADBEEFULL, 0xFEEDFACEFEEDFACEULL});   // poison
         // GWSIM_NOCACHE=1: the lane re-reads its state from the work area before every slice; GWSIM_SPILL=n: the lane is written back
         // and re-read every n slices (as the flow kernel does around its out-of-line continuations). Neither may change any result.
+        // GWSIM_PROMOTE="n1,n2": running reads whose work area is nearly full move into one of n1 blocks of 8 x slab_words words and from
+        // there into one of n2 blocks of 64 x slab_words words, as in the flow kernel (gw_promote_*); when the blocks run out the reads
+        // fall back to the passes with larger work areas. No result may depend on any of this.
+        GwExtPool pool;
+        memset(&pool, 0, sizeof pool);
+        std::vector<u64> pool_mem1, pool_mem2;
+        if (const char* pe = getenv("GWSIM_PROMOTE")) {
+            unsigned n1 = 0, n2 = 0;
+            sscanf(pe, "%u,%u", &n1, &n2);
+            pool.block_words = slab_words * 8; pool.n_blocks = n1;
+            pool.block_words2 = slab_words * 64; pool.n_blocks2 = n2;
+            pool_mem1.assign((size_t)n1 * pool.block_words + 2, 0xDEADBEEFDEADBEEFULL);
+            pool_mem2.assign((size_t)n2 * pool.block_words2 + 2, 0xDEADBEEFDEADBEEFULL);
+            pool.base = pool_mem1.data(); pool.base2 = pool_mem2.data();
+            bv.ext_pool = &pool;
+        }
         const bool nocache = getenv("GWSIM_NOCACHE") && atoi(getenv("GWSIM_NOCACHE"));
         const int spill = getenv("GWSIM_SPILL") ? atoi(getenv("GWSIM_SPILL")) : 0;
         auto verify_pending = [&](const GwSlab& s) {   // what a verification batch of the flow kernel does for one parked read
@@ -138,6 +155,13 @@ char* gwsim_align(void* h, const double* cfgv, uint32_t n_reads, const char* bas
                 while (r == GW_STEP_CONTINUE) {
                     if (nocache && ln.mid == 0) ln.cached = -1;
                     if (spill && ++slices % spill == 0) { gw_lane_flush(s, ln); gw_lane_reload(s, ln); }
+                    if (ln.mid == 0 && gw_wants_promotion(s, (uint32_t)ln.top, ln.k, ln.qn)) {   // as the flow kernel does before a slice
+                        gw_lane_flush(s, ln);
+                        if (u64* nb = gw_promote_take(s)) {
+                            gw_promote_copy(s.base, nb, (uint32_t)ln.top, 0u, 1u);
+                            gw_promote_commit(s, nb, &slabs[slot]);
+                        }
+                    }
                     if (ln.mid == 0) r = gw_lane_poll(env, s, ln);
                     if (r == GW_STEP_CONTINUE && ln.mid == GW_MID_TRY)   // as the flow kernel: the specialised form for states that head no split chain
                         r = gw_lane_is_exclusive(ln) ? gw_lane_try<MAXH, true>(env, s, ln) : gw_lane_try<MAXH, false>(env, s, ln);

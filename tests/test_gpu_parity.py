@@ -228,7 +228,11 @@ def test_sam_parity_large_work_areas_in_chunks(small):
 
 
 @pytest.mark.parametrize("opts", [dict(slab_words=1024, ext_mult=2), dict(slab_words=1024, ext_pct=1, ext_mult=7), dict(slab_words=768, ext_mult=1),
-                                  dict(slab_words=1024, ext_pct=0), dict(slab_words=1024, ext_mult=3)])
+                                  dict(slab_words=1024, ext_pct=0), dict(slab_words=1024, ext_mult=3),
+                                  dict(slab_words=1024, ext_mult=2, big_slab_words=8192, ext2_pm=500),
+                                  dict(slab_words=1024, ext_pct=2, ext_mult=2, big_slab_words=16384, ext2_pm=3),
+                                  dict(slab_words=768, ext_mult=1, big_slab_words=4096, ext2_pm=1000), dict(slab_words=1024, ext2_pm=0),
+                                  dict(mem_budget_mb=64), dict(mem_budget_mb=8, wave_reads=500)])
 def test_sam_parity_moves_to_larger_work_areas(small, opts):
     # a read whose work area is nearly full is moved into a larger block taken from a pool and goes on there; when the pool is empty,
     # the block fills up too or the queue overflows, the read is run again from the start with a larger work area: the outcome must
@@ -341,5 +345,21 @@ def test_config5_read_length_sweep_5mbp(tmp_path):
     idx, oidx = gw.FMIndexOnGenome.load(fa, 0), O.OracleIndex.load(fa)
     for L in (36, 50, 75, 100, 125, 150, 200, 250):
         compare(idx, oidx, synth.simulate_reads(lc, 2000, L, 3, 15 + L), gw.AlignmentConfig(k=3, reportType="allhits"), dict(k=3, report_type=1))
+    idx.close()
+    oidx.close()
+
+
+def test_extended_k5_low_complexity_small_work_areas(tmp_path):
+    # long reads with k = 5 on a low-complexity genome, ALLHITS, first work areas of 8 KB: most reads move into a block of the first size,
+    # many from there into one of the second (their queue moves to the end of the block each time), the rest is run again in the passes
+    # with larger work areas; the extended domain is on because part of these (m, k) make the reference's StaircaseFilter throw
+    lc = synth.low_complexity_genome(400_000, 9)
+    fa = str(tmp_path / "lc.fa")
+    synth.write_fasta(fa, [("lc", lc)])
+    gw.bwt(fa, 0)
+    idx, oidx = gw.FMIndexOnGenome.load(fa, 0), O.OracleIndex.load(fa)
+    reads = synth.simulate_reads(lc, 1200, 200, 5, 31) + synth.simulate_reads(lc, 800, 120, 4, 32)
+    for opts in (dict(slab_words=1024), dict(slab_words=1024, ext_pct=3, ext2_pm=5), dict()):
+        compare(idx, oidx, reads, gw.AlignmentConfig(k=5, reportType="allhits", extended=True), dict(k=5, report_type=1, extended=1), **opts)
     idx.close()
     oidx.close()

@@ -149,3 +149,24 @@ def test_verifier_many_differences_and_unrelated_windows():
         assert (a is None) == (b is None), (ref, q)
         if a:
             assert (a["cigar"], a["pos"], a["nm"]) == (b["cigar"], b["pos"], b["nm"]), (ref, q)
+
+
+@pytest.mark.parametrize("blocks", ["0,0", "1000,1000", "40,3", "0,50"])
+def test_moving_into_larger_work_areas_while_running(tmp_path, monkeypatch, blocks):
+    # gw_promote_*: a read whose work area is nearly full moves into a block 8 x as large and from there into one 64 x as large; when no
+    # block is left it runs until its work area is full and is run again from the start with a larger one. Small first work areas,
+    # repeat-rich and low-complexity genomes, ALLHITS: every read goes through some of this, and no result may depend on which part.
+    monkeypatch.setenv("GWSIM_PROMOTE", blocks)
+    g = synth.inject_repeats(synth.random_genome(40_000, 21), 22, families=4, min_len=200, max_len=600, copies=(5, 20))
+    lc = synth.low_complexity_genome(40_000, 23)
+    fa, oi, si = _mk(tmp_path, "m.fa", [("rep", g), ("low", lc)])
+    import numpy as np
+    both = np.concatenate([g, lc])
+    for cfg, reads in ((dict(k=3, report_type=1), synth.simulate_reads(both, 250, 100, 3, 24)),
+                       (dict(k=3), synth.simulate_reads(both, 150, 150, 3, 25)),
+                       (dict(k=5, report_type=1, extended=1), synth.simulate_reads(both, 60, 200, 5, 26))):
+        ro, rs = _compare(oi, si, reads, slab_words=1024, **cfg)
+        if blocks == "0,0":
+            assert rs["overflow_reads"] > 0   # the workload does leave the first work area
+    oi.close()
+    si.close()
