@@ -137,8 +137,11 @@ int gw_aligner_last_timing(const gw_aligner_t*, float ms[6]);
  * [first, first+n) of the last gw_align_batch* call: out[4*i..] = numFMIndexSearches, numSW, numCutOff, numFiltered */
 int gw_aligner_read_counters(const gw_aligner_t*, uint32_t first, uint32_t n, uint32_t* out);
 
-/* tunables of an aligner (all optional): "scan_coop" 0/1 (4-lane cooperative quick scan, default 1), "slab_words" (8-byte words of the
- * per-read work area of the first pass), "big_slab_words" (second pass), "wave_reads" (reads resident per wave) */
+/* tunables of an aligner (all optional; none changes a result — INTEGRATION.md has the table): "scan_coop" 0/1 (4-lane cooperative quick
+ * scan, default 1), "slab_words" (8-byte words of a read's first work area; 0 = chosen from the batch), "big_slab_words" (largest work
+ * area), "ext_pct" / "ext_mult" / "ext2_pm" (blocks running reads can move into), "mem_budget_mb" / "tier_budget_mb" (device memory for
+ * work areas; 0 = from the free memory), "wave_reads" (upper bound of the reads resident per wave), "flow_order", "flow_fetch",
+ * "flow_batch", "flow_age", "flow_flush", "flow_blocks" (flow kernel), "l2_persist_mb". Unknown names return GW_E_ARG. */
 int gw_aligner_set_option(gw_aligner_t*, const char* name, int64_t value);
 
 /* AlignmentRecord.convert + toSAMLine + SAMOutput.emit (align/record/AlignmentRecord.java:92-276, align/SAMOutput.java:72-82) for the hit
