@@ -1,5 +1,5 @@
-"""Per-pass times of the flow kernel (first pass and the passes with larger work areas) for one batch of a bench config; needs GW_TRACE=1.
-usage (GPU box): GW_TRACE=1 python tools/trace_passes.py --config 4 --reads 250000 [opt=value ...]"""
+"""Per-pass times of the flow kernel (first pass and the passes with larger work areas) for one batch of a bench config (aligner option trace=1).
+usage (GPU box): python tools/trace_passes.py --config 4 --reads 250000 [opt=value ...]"""
 import argparse
 import os
 import sys
@@ -22,6 +22,7 @@ idx = gw.FMIndexOnGenome.load(fa, 0)
 reads = [r.tobytes().decode() for g in bench.make_reads(spec, genome, 0) for r in g]
 cfg = gw.AlignmentConfig(k=spec["k"], reportType=spec["report"], extended=spec["extended"])
 opts = {kv.split("=")[0]: int(kv.split("=")[1]) for kv in a.opts}
+opts["trace"] = 1
 bsf = gw.BidirectionalSuffixFilter(idx, cfg, **opts)
 bsf.align(reads[:20000])
 sys.stderr.write("---- timed batch, options %r\n" % opts)
