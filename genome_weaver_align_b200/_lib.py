@@ -54,6 +54,7 @@ SYMBOLS = {
     "gw_aligner_destroy": (None, [_P]),
     "gw_aligner_set_option": (C.c_int, [_P, C.c_char_p, C.c_int64]),
     "gw_align_batch": (C.c_int, [_P, _P, _P, C.c_uint32, _P, C.POINTER(C.c_uint64), _P, C.POINTER(C.c_uint64), C.POINTER(Counters)]),
+    "gw_align_batch_fetch": (C.c_int, [_P, _P, C.POINTER(C.c_uint64), _P, C.POINTER(C.c_uint64)]),
     "gw_align_batch_device": (C.c_int, [_P, _P, _P, C.c_uint32, C.c_uint64, C.c_uint32, _P, C.c_uint64, _P, C.c_uint64, C.POINTER(C.c_uint64),
                                         C.POINTER(C.c_uint64), C.POINTER(Counters)]),
     "gw_aligner_read_counters": (C.c_int, [_P, C.c_uint32, C.c_uint32, _P]),

@@ -190,9 +190,12 @@ class BidirectionalSuffixFilter:
             cig = np.zeros(cap_c, dtype=np.uint32)
             nh, nc = C.c_uint64(cap_h), C.c_uint64(cap_c)
             rc = L.lib().gw_align_batch(self._h, L.ptr(b), L.ptr(off), n, L.ptr(hits), C.byref(nh), L.ptr(cig), C.byref(nc), C.byref(cnt))
-            if rc == L.GW_E_CAPACITY:
+            if rc == L.GW_E_CAPACITY:   # the batch is aligned and its records are retained on the device: fetch them into larger buffers
                 cap_h, cap_c = int(nh.value) + 16, int(nc.value) + 64
-                continue
+                hits = np.zeros(cap_h, dtype=L.HIT_DTYPE)
+                cig = np.zeros(cap_c, dtype=np.uint32)
+                nh, nc = C.c_uint64(cap_h), C.c_uint64(cap_c)
+                rc = L.lib().gw_align_batch_fetch(self._h, L.ptr(hits), C.byref(nh), L.ptr(cig), C.byref(nc))
             L.check(rc)
             break
         ms = (C.c_float * 6)()

@@ -416,7 +416,11 @@ void worker(int device, const Options* o, Channel<BatchPtr>* in, Channel<BatchPt
                 b->nh = b->hits.size(); b->nc = b->cig.size();
                 rc = gw_align_batch(al, b->bases.data(), b->base_off.data(), b->n, b->hits.data(), &b->nh, b->cig.data(), &b->nc, &b->counters);
                 if (rc != GW_E_CAPACITY) break;
+                // the batch is aligned, only the buffers were too small: fetch the retained records instead of aligning again
                 b->hits.resize(b->nh + 16); b->cig.resize(b->nc + 64);
+                b->nh = b->hits.size(); b->nc = b->cig.size();
+                rc = gw_align_batch_fetch(al, b->hits.data(), &b->nh, b->cig.data(), &b->nc);
+                break;
             }
             if (rc != GW_OK) fail("align");
             else {

@@ -122,6 +122,11 @@ void gw_aligner_destroy(gw_aligner_t*);
  * With GW_E_CAPACITY the required sizes are written to *n_hits / *n_cigar and nothing else is valid. */
 int gw_align_batch(gw_aligner_t*, const char* bases, const uint64_t* offsets, uint32_t n_reads, gw_hit_t* hits,
                    uint64_t* n_hits, uint32_t* cigar_ops, uint64_t* n_cigar, gw_counters_t* counters);
+/* No counterpart in the reference (its Reporter is called once per alignment): the hit records of this aligner's LAST gw_align_batch call,
+ * copied out again. For the caller that got GW_E_CAPACITY: enlarge the buffers to the sizes written back and fetch, instead of aligning the
+ * batch a second time. Same meaning of n_hits / n_cigar (in: capacity, out: count). GW_E_ARG when nothing is retained (no batch yet, the
+ * last batch failed, or gw_align_batch_device was called since). */
+int gw_align_batch_fetch(gw_aligner_t*, gw_hit_t* hits, uint64_t* n_hits, uint32_t* cigar_ops, uint64_t* n_cigar);
 
 /* Same path with inputs already resident in HBM of the aligner's device (device pointers), results left on the device:
  * used to time the kernels without host<->device copies. d_hits/d_cigar capacities in elements. Returns counts via host ptrs. */

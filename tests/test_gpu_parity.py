@@ -363,3 +363,27 @@ def test_extended_k5_low_complexity_small_work_areas(tmp_path):
         compare(idx, oidx, reads, gw.AlignmentConfig(k=5, reportType="allhits", extended=True), dict(k=5, report_type=1, extended=1), **opts)
     idx.close()
     oidx.close()
+
+
+def test_fetch_after_capacity_error(small):
+    # gw_align_batch with output buffers that are too small returns GW_E_CAPACITY and the sizes needed; gw_align_batch_fetch then hands
+    # out the retained records of that batch (the batch is not aligned again) and they are what a call with large buffers returns
+    import ctypes as C
+    from genome_weaver_align_b200 import _lib as L
+    reads = synth.simulate_reads(small["g"], 400, 100, 3, 83)
+    bsf = gw.BidirectionalSuffixFilter(small["idx"], gw.AlignmentConfig(k=3))
+    want = bsf.align(reads)
+    b, off = L.concat(reads)
+    hits, cig = np.zeros(4, dtype=L.HIT_DTYPE), np.zeros(4, dtype=np.uint32)
+    nh, nc = C.c_uint64(4), C.c_uint64(4)
+    cnt = L.Counters()
+    rc = L.lib().gw_align_batch(bsf._h, L.ptr(b), L.ptr(off), len(reads), L.ptr(hits), C.byref(nh), L.ptr(cig), C.byref(nc), C.byref(cnt))
+    assert rc == L.GW_E_CAPACITY and nh.value == len(want.hits) and nc.value == len(want.cigars)
+    searches = cnt.fm_searches
+    hits, cig = np.zeros(nh.value, dtype=L.HIT_DTYPE), np.zeros(nc.value, dtype=np.uint32)
+    rc = L.lib().gw_align_batch_fetch(bsf._h, L.ptr(hits), C.byref(nh), L.ptr(cig), C.byref(nc))
+    assert rc == 0 and hits.tobytes() == want.hits.tobytes() and cig.tobytes() == want.cigars.tobytes()
+    assert cnt.fm_searches == searches == want.counters["fm_searches"]
+    nh2, nc2 = C.c_uint64(1), C.c_uint64(1)
+    assert L.lib().gw_align_batch_fetch(bsf._h, L.ptr(hits), C.byref(nh2), L.ptr(cig), C.byref(nc2)) == L.GW_E_CAPACITY and nh2.value == nh.value
+    bsf.close()
