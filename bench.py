@@ -445,11 +445,11 @@ def run_ours(args):
         gather = None
         if lib.gw_gather_benchmark(idx._h, 1, 1 << 28, 3, C.byref(gbs), C.byref(gms)) == 0:
             gather = float(gbs.value)
-        traffic = None
+        traffic, traffic_at = None, None
         try:   # DRAM bytes per step of the dominant kernel family from the committed ncu --set full capture (profiles/)
             tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
             if tj.get("reads") == n and tj.get("genome_bp") == spec["genome_bp"]:
-                traffic = tj["dram_bytes_per_step"]
+                traffic, traffic_at = tj["dram_bytes_per_step"], tj.get("git_head")   # a capture, not measured in this run: it says of which build
         except Exception:  # noqa: BLE001
             pass
         value = world * n * args.steps / dev_time
@@ -461,7 +461,7 @@ def run_ours(args):
                            l2="working set (index %.2f GB + per-read work areas of several GB rewritten every step) exceeds the 126 MB L2; no explicit flush" % index_gb,
                            parallelism="reads sharded over %d GPU(s), index replicated, no collective" % world, index_built_by=how,
                            index_build_s=round(t_build, 2), index_open_s=round(t_open, 2), locate_table_step=idx.locateStep()),
-            "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_captured_at_git_head": traffic_at,
                          "peak_source": peak_src, "random_gather_gbs": gather, "frac_of_random_gather": (ach / gather if gather else None),
                          "note": "algorithmic bytes = occurrence-table lookups the kernel did x 64 B (+4 B per locate) over the CUDA-event time of the "
                                  "kernel family; with the dense locate table a locate is one 4-byte gather, so the lookups of the reference's "
