@@ -98,3 +98,16 @@ def test_exported_symbols_match_the_header():
     exported = set(re.findall(r"\bT (gw_[a-z0-9_]+)\b", nm))
     assert declared <= exported, declared - exported
     _lib.lib()   # loads, and every declared symbol resolves with its signature
+
+
+def test_no_alloc_verifier_checks_its_limit_before_touching_the_device():
+    # gw_verify_pairs_noalloc (no counterpart in the reference): a batch whose DP history does not fit the static device array is refused
+    # with GW_E_ARG and a message, before any CUDA call (so this holds on a machine without a GPU too)
+    from genome_weaver_align_b200 import _lib
+    lib = _lib.lib()
+    n = (64 << 20) // ((106 + 2) * 2 * 16) + 1
+    rc = lib.gw_verify_pairs_noalloc(0, None, 1, 1, 1, 1, n, 106, 100, 3, 1, 1, 40)   # (the pointers only need to be non-null: nothing is read)
+    assert rc == _lib.GW_E_ARG
+    msg = lib.gw_last_error().decode()
+    assert "static scratch" in msg and str(n) in msg
+    assert lib.gw_verify_pairs_noalloc(0, None, 1, 1, 1, 1, 10, 5000, 100, 3, 1, 1, 40) == _lib.GW_E_ARG   # window longer than supported
