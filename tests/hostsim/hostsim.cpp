@@ -32,6 +32,7 @@ GwSlabParams slab_params(uint32_t words) {   // same rule as gw_api_align.inc
     sp.slab_words = words;
     sp.queue_cap = std::max<uint32_t>(64, std::min<uint32_t>(words / 16, 8192));
     sp.hit_cap = std::max<uint32_t>(32, std::min<uint32_t>(words / 64, 2048));
+    if (const char* hc = getenv("GWSIM_HITCAP")) sp.hit_cap = (uint32_t)std::max(1, atoi(hc));   // tiny hit lists: they must grow (gw_add_result)
     sp.queue_at = 0;
     return sp;
 }

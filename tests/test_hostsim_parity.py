@@ -170,3 +170,19 @@ def test_moving_into_larger_work_areas_while_running(tmp_path, monkeypatch, bloc
             assert rs["overflow_reads"] > 0   # the workload does leave the first work area
     oi.close()
     si.close()
+
+
+def test_hit_list_grows_in_the_arena(tmp_path, monkeypatch):
+    # gw_add_result: a full hit list moves into the arena with twice the capacity. The simulator starts every read with room for ONE hit
+    # (GWSIM_HITCAP), so every read that reports a split pair or several equally good alignments goes through it, some of them repeatedly.
+    monkeypatch.setenv("GWSIM_HITCAP", "1")
+    g = synth.inject_repeats(synth.random_genome(40_000, 41), 42, families=4, min_len=150, max_len=500, copies=(6, 20))
+    fa, oi, si = _mk(tmp_path, "h.fa", [("c", g)])
+    reads = synth.simulate_reads(g, 300, 100, 3, 43)
+    cut = 45
+    reads += [g[1000:1000 + cut].tobytes().decode() + g[9000:9000 + 100 - cut].tobytes().decode() for _ in range(3)]   # split alignments
+    for cfg in (dict(k=3, report_type=1), dict(k=3, report_type=2, top_l=4), dict(k=3)):
+        ro, rs = _compare(oi, si, reads, **cfg)
+        assert max(len(x) for x in ro["sam"]) >= 2   # some read does report more than one record
+    oi.close()
+    si.close()
