@@ -289,8 +289,9 @@ def run_reference(args):
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1000.0 * sum(times) / len(times), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64",
-        "data": "synthetic", "config": dict(workload=spec["name"] + " (CPU oracle; the JVM reference cannot run here)",
-                                            **dict(workload(spec), reads_per_step=n_sample, reads_in_workload=spec["reads"])),
+        "data": "synthetic", "config": dict(workload=spec["name"], **dict(workload(spec), reads_per_step=n_sample, reads_in_workload=spec["reads"],
+                                                                          note="C++ oracle of the reference path on the host cores, a bounded sample of the "
+                                                                               "workload per step (the JVM reference cannot run here)")),
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample_desc},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "index_built_by": how}))
 
