@@ -109,7 +109,10 @@ int64_t gw_index_contig_offset(const gw_index_t*, int32_t i);
 int gw_index_device(const gw_index_t*);
 
 void gw_config_default(gw_config_t*);
-/* new BidirectionalSuffixFilter(fmIndex, reference, config) (align/strategy/BidirectionalSuffixFilter.java:97-102) */
+/* new BidirectionalSuffixFilter(fmIndex, reference, config) (align/strategy/BidirectionalSuffixFilter.java:97-102).
+ * Device memory: at its first batch an aligner measures the free memory of its device and plans its work areas within it (up to about
+ * 90 %; buffers are allocated as batches need them and kept until gw_aligner_destroy). Option "mem_budget_mb" sets a smaller budget, e.g.
+ * for several aligners on one device. */
 int gw_aligner_create(const gw_index_t*, const gw_config_t*, gw_aligner_t** out);
 void gw_aligner_destroy(gw_aligner_t*);
 
@@ -135,7 +138,8 @@ int gw_align_batch_device(gw_aligner_t*, const char* d_bases, const uint64_t* d_
                           uint64_t* n_hits, uint64_t* n_cigar, gw_counters_t* counters);
 
 /* milliseconds spent in device work of the last gw_align_batch* call per kernel family, measured with CUDA events on the
- * aligner's stream: [0] prep+quick-scan, [1] search, [2] locate, [3] verify, [4] finalize, [5] whole batch */
+ * aligner's stream: [0] prep + quick scan + work order, [1] flow kernel (search + locate + verify, all passes), [2] and [3] unused (0),
+ * [4] emit, [5] whole batch */
 int gw_aligner_last_timing(const gw_aligner_t*, float ms[6]);
 
 /* the reference's per-read debug counters (align/strategy/BidirectionalSuffixFilter.java:224-233, :588-592) of reads
